@@ -1,0 +1,290 @@
+"""ekf_slam_b200 - Python host mirror of the C ABI (include/ekf_slam_b200.h).
+
+The product is the sm_100a shared library `libekf_slam_b200.so` next to this file; this module
+only binds it with ctypes so that tests and bench.py can drive it.  There is NO fallback: if the
+library is missing or no B200 is present, construction raises.
+
+The directory is called `ekf-slam_b200` (repo convention); import it as `ekf_slam_b200` through
+the loader at the repo root (`import ekf_slam_b200`), see /ekf_slam_b200.py.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libekf_slam_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "ekf_slam_b200.h")
+
+EKF_OK, EKF_ERR_INVALID, EKF_ERR_CAPACITY, EKF_ERR_EMPTY_SCAN, EKF_ERR_BAD_ID, EKF_ERR_CUDA, \
+    EKF_ERR_NO_DEVICE, EKF_ERR_NOMEM = range(8)
+
+MARKER_ADD, MARKER_DELETE = 0, 2
+
+
+class EkfError(RuntimeError):
+    def __init__(self, status: int, where: str, detail: str = ""):
+        self.status = status
+        super().__init__(f"{where}: status {status} ({status_string(status)}) {detail}".strip())
+
+
+class EkfConfig(C.Structure):
+    _fields_ = [("n_landmarks", C.c_int32), ("q_noise", C.c_double), ("r_noise", C.c_double),
+                ("mah_threshold", C.c_double), ("prior", C.c_double), ("device", C.c_int32),
+                ("max_scan", C.c_int32), ("shard_rank", C.c_int32), ("shard_count", C.c_int32)]
+
+
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compile the library in-tree with nvcc for sm_100a (ekf-slam_b200/Makefile)."""
+    if force:
+        subprocess.check_call(["make", "-C", _HERE, "clean"], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", _HERE], stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+def load() -> C.CDLL:
+    """Load the C-ABI library; raises if it was never built (no silent fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(f"{LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, dp, ip = C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32)
+    u8p = C.POINTER(C.c_uint8)
+    i32, i64p = C.c_int32, C.POINTER(C.c_int64)
+    sigs = {
+        "ekf_default_config": (None, [C.POINTER(EkfConfig)]),
+        "ekf_status_string": (C.c_char_p, [C.c_int]),
+        "ekf_version": (C.c_char_p, []),
+        "ekf_create": (C.c_int, [C.POINTER(EkfConfig), C.POINTER(vp)]),
+        "ekf_destroy": (C.c_int, [vp]),
+        "ekf_set_stream": (C.c_int, [vp, vp]),
+        "ekf_synchronize": (C.c_int, [vp]),
+        "ekf_last_status": (C.c_int, [vp]),
+        "ekf_last_cuda_error": (C.c_char_p, [vp]),
+        "ekf_predict": (C.c_int, [vp, C.c_double, C.c_double, C.c_double]),
+        "ekf_update_known": (C.c_int, [vp, i32, ip, dp, u8p]),
+        "ekf_update_unknown": (C.c_int, [vp, i32, dp, ip, ip]),
+        "ekf_scan_dev": (C.c_int, [vp, vp, i32, vp, vp, vp, vp]),
+        "ekf_scan": (C.c_int, [vp, dp, i32, dp, ip, u8p, ip, ip, dp]),
+        "ekf_state_dim": (C.c_int, [vp, ip]),
+        "ekf_get_pose": (C.c_int, [vp, dp]),
+        "ekf_get_state": (C.c_int, [vp, dp, i32]),
+        "ekf_get_count": (C.c_int, [vp, ip]),
+        "ekf_get_landmarks": (C.c_int, [vp, dp, i32, ip]),
+        "ekf_get_sigma_block": (C.c_int, [vp, i32, i32, i32, i32, dp]),
+        "ekf_set_state": (C.c_int, [vp, dp, i32]),
+        "ekf_set_count": (C.c_int, [vp, i32]),
+        "ekf_set_previous_xy": (C.c_int, [vp, C.c_double, C.c_double]),
+        "ekf_get_previous_xy": (C.c_int, [vp, dp]),
+        "ekf_set_sigma_block": (C.c_int, [vp, i32, i32, i32, i32, dp]),
+        "ekf_fill_procedural": (C.c_int, [vp, C.c_uint64, i32, i32]),
+        "ekf_sigma_storage": (C.c_int, [vp, i64p, i64p]),
+        "ekf_launch_count": (C.c_int, [vp, i64p]),
+        "ekf_last_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+        "ekf_enable_timing": (C.c_int, [vp, i32]),
+    }
+    for name, (res, args) in sigs.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def status_string(status: int) -> str:
+    return load().ekf_status_string(int(status)).decode()
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+class EkfSlam:
+    """One EKF-SLAM filter on one B200.  Method names follow the C ABI; argument meaning and
+    error behaviour follow the reference callbacks (nuslam/src/slam.cpp:180-316, 318-530)."""
+
+    def __init__(self, n_landmarks: int = 50, q_noise: float = 1.0e-2, r_noise: float = 1.0e-2,
+                 mah_threshold: float = 2.0, prior: float = 10e6, device: int = -1, max_scan: int = 0):
+        self._L = load()
+        cfg = EkfConfig()
+        self._L.ekf_default_config(C.byref(cfg))
+        cfg.n_landmarks, cfg.q_noise, cfg.r_noise = n_landmarks, q_noise, r_noise
+        cfg.mah_threshold, cfg.prior, cfg.device, cfg.max_scan = mah_threshold, prior, device, max_scan
+        h = C.c_void_p()
+        rc = self._L.ekf_create(C.byref(cfg), C.byref(h))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_create")
+        self._h = h
+        self.n_landmarks = n_landmarks
+        self.n = 3 + 2 * n_landmarks
+
+    # -- lifetime ---------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ekf_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc: int, where: str, allow=()):
+        if rc != EKF_OK and rc not in allow:
+            detail = self._L.ekf_last_cuda_error(self._h).decode() if rc == EKF_ERR_CUDA else ""
+            raise EkfError(rc, where, detail)
+        return rc
+
+    def set_stream(self, cuda_stream_ptr: int):
+        self._check(self._L.ekf_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "ekf_set_stream")
+
+    def synchronize(self):
+        self._check(self._L.ekf_synchronize(self._h), "ekf_synchronize")
+
+    def last_status(self) -> int:
+        return self._L.ekf_last_status(self._h)
+
+    # -- the scan update --------------------------------------------------------------------------
+    def predict(self, theta: float, x: float, y: float):
+        self._check(self._L.ekf_predict(self._h, float(theta), float(x), float(y)), "ekf_predict")
+
+    def update_known(self, ids, xy, action=None):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1)
+        act = None
+        if action is not None:
+            action = np.ascontiguousarray(action, dtype=np.uint8)
+            act = action.ctypes.data_as(C.POINTER(C.c_uint8))
+        self._check(self._L.ekf_update_known(self._h, len(ids), _ip(ids), _dp(xy), act), "ekf_update_known")
+
+    def update_unknown(self, xy, allow_capacity_error: bool = False):
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1)
+        m = len(xy) // 2
+        assoc = np.full(m, -7, dtype=np.int32)
+        cnt = C.c_int32(0)
+        rc = self._L.ekf_update_unknown(self._h, m, _dp(xy), _ip(assoc), C.byref(cnt))
+        self._check(rc, "ekf_update_unknown", allow=(EKF_ERR_CAPACITY,) if allow_capacity_error else ())
+        return assoc
+
+    def scan(self, pose, xy, ids=None, action=None):
+        """predict + update in one call; returns (assoc, count, pose_after)."""
+        pose = np.ascontiguousarray(pose, dtype=np.float64)
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1)
+        m = len(xy) // 2
+        idp = actp = None
+        if ids is not None:
+            ids = np.ascontiguousarray(ids, dtype=np.int32)
+            idp = _ip(ids)
+        if action is not None:
+            action = np.ascontiguousarray(action, dtype=np.uint8)
+            actp = action.ctypes.data_as(C.POINTER(C.c_uint8))
+        assoc = np.full(m, -7, dtype=np.int32)
+        cnt = C.c_int32(0)
+        out_pose = np.zeros(3)
+        self._check(self._L.ekf_scan(self._h, _dp(pose), m, _dp(xy), idp, actp, _ip(assoc), C.byref(cnt),
+                                     _dp(out_pose)), "ekf_scan")
+        return assoc, int(cnt.value), out_pose
+
+    def scan_dev(self, pose_ptr: int, m: int, xy_ptr: int, ids_ptr: int = 0, action_ptr: int = 0,
+                 assoc_ptr: int = 0):
+        """asynchronous scan from raw device pointers (ints)."""
+        vp = C.c_void_p
+        self._check(self._L.ekf_scan_dev(self._h, vp(pose_ptr), m, vp(xy_ptr), vp(ids_ptr or None),
+                                         vp(action_ptr or None), vp(assoc_ptr or None)), "ekf_scan_dev")
+
+    # -- accessors ----------------------------------------------------------------------------------
+    @property
+    def count(self) -> int:
+        c = C.c_int32(0)
+        self._check(self._L.ekf_get_count(self._h, C.byref(c)), "ekf_get_count")
+        return int(c.value)
+
+    @count.setter
+    def count(self, value: int):
+        self._check(self._L.ekf_set_count(self._h, int(value)), "ekf_set_count")
+
+    def pose(self) -> np.ndarray:
+        out = np.zeros(3)
+        self._check(self._L.ekf_get_pose(self._h, _dp(out)), "ekf_get_pose")
+        return out
+
+    def state(self, n: int | None = None) -> np.ndarray:
+        n = self.n if n is None else n
+        out = np.zeros(n)
+        self._check(self._L.ekf_get_state(self._h, _dp(out), n), "ekf_get_state")
+        return out
+
+    def set_state(self, values):
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        self._check(self._L.ekf_set_state(self._h, _dp(values), len(values)), "ekf_set_state")
+
+    def landmarks(self) -> np.ndarray:
+        c = self.count
+        out = np.zeros((max(c, 1), 2))
+        cc = C.c_int32(0)
+        self._check(self._L.ekf_get_landmarks(self._h, _dp(out), c, C.byref(cc)), "ekf_get_landmarks")
+        return out[:c]
+
+    def sigma_block(self, i0: int, i1: int, j0: int, j1: int) -> np.ndarray:
+        out = np.zeros((i1 - i0, j1 - j0))
+        self._check(self._L.ekf_get_sigma_block(self._h, i0, i1, j0, j1, _dp(out)), "ekf_get_sigma_block")
+        return out
+
+    def sigma(self) -> np.ndarray:
+        return self.sigma_block(0, self.n, 0, self.n)
+
+    def set_sigma_block(self, i0: int, j0: int, block):
+        block = np.ascontiguousarray(block, dtype=np.float64)
+        i1, j1 = i0 + block.shape[0], j0 + block.shape[1]
+        self._check(self._L.ekf_set_sigma_block(self._h, i0, i1, j0, j1, _dp(block)), "ekf_set_sigma_block")
+
+    def set_sigma(self, full):
+        self.set_sigma_block(0, 0, full)
+
+    def set_previous_xy(self, x: float, y: float):
+        self._check(self._L.ekf_set_previous_xy(self._h, float(x), float(y)), "ekf_set_previous_xy")
+
+    def previous_xy(self) -> np.ndarray:
+        out = np.zeros(2)
+        self._check(self._L.ekf_get_previous_xy(self._h, _dp(out)), "ekf_get_previous_xy")
+        return out
+
+    def fill_procedural(self, seed: int, count: int, grid_w: int):
+        self._check(self._L.ekf_fill_procedural(self._h, C.c_uint64(seed), count, grid_w), "ekf_fill_procedural")
+
+    def storage(self):
+        a, b = C.c_int64(0), C.c_int64(0)
+        self._check(self._L.ekf_sigma_storage(self._h, C.byref(a), C.byref(b)), "ekf_sigma_storage")
+        return int(a.value), int(b.value)
+
+    def launch_count(self) -> int:
+        a = C.c_int64(0)
+        self._check(self._L.ekf_launch_count(self._h, C.byref(a)), "ekf_launch_count")
+        return int(a.value)
+
+    def enable_timing(self, on: bool = True):
+        self._check(self._L.ekf_enable_timing(self._h, int(on)), "ekf_enable_timing")
+
+    def last_timing(self):
+        a, b = C.c_float(0), C.c_float(0)
+        self._check(self._L.ekf_last_timing(self._h, C.byref(a), C.byref(b)), "ekf_last_timing")
+        return float(a.value), float(b.value)

@@ -1,0 +1,141 @@
+// C ABI of the B200-native EKF-SLAM core (include/ekf_slam_b200.h): host-side orchestration of
+// the sm_100a kernels.  No CPU fallback exists anywhere in this file: every entry point drives
+// CUDA kernels and reports EKF_ERR_CUDA / EKF_ERR_NO_DEVICE when it cannot.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <string>
+
+#include "../../include/ekf_slam_b200.h"
+#include "ekf_downdate.cuh"
+#include "ekf_layout.h"
+#include "ekf_seq.cuh"
+#include "ekf_util.cuh"
+
+using namespace ekf;
+
+struct ekf_filter {
+  ekf_config cfg{};
+  int device = 0;
+  int num_sms = 0;
+  int N = 0, n = 0, n_int = 0, n_pad = 0, kmax = kMaxK2;
+  int64_t sigma_elems = 0;
+  // device storage
+  double *sigma = nullptr, *mu = nullptr, *W = nullptr, *V = nullptr;
+  double4 *Pp = nullptr, *D = nullptr;
+  int *cnt = nullptr, *status = nullptr;
+  double *prev_xy = nullptr;
+  unsigned long long *bar = nullptr;
+  unsigned long long bar_base = 0;
+  double *slot_d = nullptr;
+  int *slot_k = nullptr;
+  // staging for the host-pointer entry points
+  unsigned char *io_dev = nullptr, *io_host = nullptr;   // inputs: pose | xy | ids | action
+  unsigned char *res_dev = nullptr, *res_host = nullptr; // results: pose | cnt | status | assoc
+  size_t io_cap = 0, res_cap = 0;
+  double *scratch_dev = nullptr;  // block get/set staging
+  size_t scratch_cap = 0;
+  // streams / events / bookkeeping
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  bool timing = false;
+  bool ev_valid = false;
+  float seq_ms = 0.f, dd_ms = 0.f;
+  int64_t launches = 0;
+  int seq_grid = 1;
+  int dd_grid = 1;
+  int latched = EKF_OK;
+  std::string cuda_err;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+int cuda_fail(ekf_filter *f, cudaError_t e, const char *what) {
+  if (f) {
+    f->cuda_err = std::string(what) + ": " + cudaGetErrorString(e);
+    f->latched = EKF_ERR_CUDA;
+  }
+  return EKF_ERR_CUDA;
+}
+
+#define CK(f, call)                                             \
+  do {                                                          \
+    cudaError_t e_ = (call);                                    \
+    if (e_ != cudaSuccess) return cuda_fail((f), e_, #call);    \
+  } while (0)
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// layout of the packed input / result staging buffers for a scan of m measurements
+struct IoLayout {
+  size_t pose, xy, ids, action, total;
+  explicit IoLayout(int m) {
+    pose = 0; xy = 24; ids = xy + (size_t)16 * m; action = ids + (size_t)4 * m;
+    total = align_up(action + (size_t)m, 16);
+  }
+};
+struct ResLayout {
+  size_t pose, cnt, status, assoc, total;
+  explicit ResLayout(int m) {
+    pose = 0; cnt = 24; status = 28; assoc = 32; total = align_up(assoc + (size_t)4 * m, 16);
+  }
+};
+
+int ensure_io(ekf_filter *f, int m) {
+  const IoLayout in(m);
+  const ResLayout res(m);
+  if (in.total > f->io_cap) {
+    if (f->io_dev) cudaFree(f->io_dev);
+    if (f->io_host) cudaFreeHost(f->io_host);
+    f->io_dev = nullptr; f->io_host = nullptr; f->io_cap = 0;
+    const size_t cap = align_up(in.total * 2, 256);
+    CK(f, cudaMalloc(&f->io_dev, cap));
+    CK(f, cudaMallocHost(&f->io_host, cap));
+    f->io_cap = cap;
+  }
+  if (res.total > f->res_cap) {
+    if (f->res_dev) cudaFree(f->res_dev);
+    if (f->res_host) cudaFreeHost(f->res_host);
+    f->res_dev = nullptr; f->res_host = nullptr; f->res_cap = 0;
+    const size_t cap = align_up(res.total * 2, 256);
+    CK(f, cudaMalloc(&f->res_dev, cap));
+    CK(f, cudaMallocHost(&f->res_host, cap));
+    f->res_cap = cap;
+  }
+  return EKF_OK;
+}
+
+int ensure_scratch(ekf_filter *f, size_t bytes) {
+  if (bytes > f->scratch_cap) {
+    if (f->scratch_dev) cudaFree(f->scratch_dev);
+    f->scratch_dev = nullptr; f->scratch_cap = 0;
+    CK(f, cudaMalloc(&f->scratch_dev, bytes));
+    f->scratch_cap = bytes;
+  }
+  return EKF_OK;
+}
+
+int env_int(const char *name, int dflt) {
+  const char *v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+}  // namespace
+
+#include "ekf_abi_lifetime.inl"
+#include "ekf_abi_scan.inl"
+#include "ekf_abi_access.inl"

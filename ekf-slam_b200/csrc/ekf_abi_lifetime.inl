@@ -1,0 +1,196 @@
+// Part of ekf_abi.cu: configuration, lifetime, stream and status entry points.
+
+extern "C" {
+
+void ekf_default_config(ekf_config *cfg) {
+  if (!cfg) return;
+  memset(cfg, 0, sizeof(*cfg));
+  cfg->n_landmarks = 50;       // slam.cpp:665
+  cfg->q_noise = 1.0e-2;       // slam.cpp:666
+  cfg->r_noise = 1.0e-2;       // slam.cpp:667
+  cfg->mah_threshold = 2.0;    // slam.cpp:671
+  cfg->prior = 10e6;           // slam.cpp:130
+  cfg->device = -1;
+  cfg->max_scan = 0;
+  cfg->shard_rank = 0;
+  cfg->shard_count = 1;
+}
+
+const char *ekf_status_string(int status) {
+  switch (status) {
+    case EKF_OK: return "ok";
+    case EKF_ERR_INVALID: return "invalid argument";
+    case EKF_ERR_CAPACITY: return "landmark capacity exceeded";
+    case EKF_ERR_EMPTY_SCAN: return "empty scan";
+    case EKF_ERR_BAD_ID: return "landmark id out of range";
+    case EKF_ERR_CUDA: return "CUDA error";
+    case EKF_ERR_NO_DEVICE: return "no usable CUDA device";
+    case EKF_ERR_NOMEM: return "out of memory";
+    default: return "unknown status";
+  }
+}
+
+const char *ekf_version(void) { return "ekf_slam_b200 0.1 (sm_100a)"; }
+
+int ekf_destroy(ekf_filter *f) {
+  if (!f) return EKF_ERR_INVALID;
+  {
+    DeviceGuard guard(f->device);
+    if (f->stream) cudaStreamSynchronize(f->stream);
+    cudaFree(f->sigma); cudaFree(f->mu); cudaFree(f->W); cudaFree(f->V);
+    cudaFree(f->Pp); cudaFree(f->D); cudaFree(f->cnt); cudaFree(f->status);
+    cudaFree(f->prev_xy); cudaFree(f->bar); cudaFree(f->slot_d); cudaFree(f->slot_k);
+    cudaFree(f->io_dev); cudaFree(f->res_dev); cudaFree(f->scratch_dev);
+    if (f->io_host) cudaFreeHost(f->io_host);
+    if (f->res_host) cudaFreeHost(f->res_host);
+    for (auto &e : f->ev) if (e) cudaEventDestroy(e);
+    if (f->own_stream) cudaStreamDestroy(f->own_stream);
+  }
+  delete f;
+  return EKF_OK;
+}
+
+int ekf_create(const ekf_config *cfg, ekf_filter **out) {
+  if (!cfg || !out) return EKF_ERR_INVALID;
+  *out = nullptr;
+  if (cfg->n_landmarks < 1 || cfg->n_landmarks > 500000000) return EKF_ERR_INVALID;
+  if (cfg->shard_count > 1) return EKF_ERR_INVALID;  // row-sharded handles: ekf_shard_* (later)
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return EKF_ERR_NO_DEVICE;
+  int dev = cfg->device;
+  if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) return EKF_ERR_NO_DEVICE;
+  if (dev >= ndev) return EKF_ERR_INVALID;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return EKF_ERR_NO_DEVICE;
+  if (prop.major < 10) return EKF_ERR_NO_DEVICE;  // sm_100a code only
+
+  ekf_filter *f = new (std::nothrow) ekf_filter();
+  if (!f) return EKF_ERR_NOMEM;
+  f->cfg = *cfg;
+  f->device = dev;
+  f->num_sms = prop.multiProcessorCount;
+  f->N = cfg->n_landmarks;
+  f->n = 3 + 2 * f->N;
+  f->n_int = ekf_n_int(f->N);
+  f->n_pad = ekf_n_pad(f->N);
+  f->sigma_elems = ekf_sigma_elems(f->n_pad);
+  DeviceGuard guard(dev);
+
+  auto fail = [&](cudaError_t e, const char *what) {
+    fprintf(stderr, "ekf_create: %s: %s\n", what, cudaGetErrorString(e));
+    ekf_destroy(f);
+    return e == cudaErrorMemoryAllocation ? EKF_ERR_NOMEM : EKF_ERR_CUDA;
+  };
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(e_, #call); } while (0)
+
+  CKC(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
+  f->stream = f->own_stream;
+  for (auto &e : f->ev) CKC(cudaEventCreate(&e));
+  const size_t panel_bytes = (size_t)f->n_pad * f->kmax * sizeof(double);
+  CKC(cudaMalloc(&f->sigma, (size_t)f->sigma_elems * sizeof(double)));
+  CKC(cudaMalloc(&f->mu, (size_t)f->n_pad * sizeof(double)));
+  CKC(cudaMalloc(&f->W, panel_bytes));
+  CKC(cudaMalloc(&f->V, panel_bytes));
+  CKC(cudaMalloc(&f->Pp, (size_t)f->n_pad * sizeof(double4)));
+  CKC(cudaMalloc(&f->D, (size_t)f->N * sizeof(double4)));
+  CKC(cudaMalloc(&f->cnt, sizeof(int)));
+  CKC(cudaMalloc(&f->status, sizeof(int)));
+  CKC(cudaMalloc(&f->prev_xy, 2 * sizeof(double)));
+  CKC(cudaMalloc(&f->bar, sizeof(unsigned long long)));
+
+  // grids: sequential kernel = cooperative, at most one CTA per SM; covariance pass = one CTA per SM
+  int seq_blocks = (f->N + kSeqThreads - 1) / kSeqThreads;
+  int max_seq = env_int("EKF_SEQ_BLOCKS", f->num_sms);
+  if (max_seq < 1) max_seq = 1;
+  if (max_seq > f->num_sms) max_seq = f->num_sms;
+  f->seq_grid = seq_blocks < max_seq ? seq_blocks : max_seq;
+  f->dd_grid = env_int("EKF_DD_BLOCKS", f->num_sms);
+  if (f->dd_grid < 1) f->dd_grid = 1;
+  CKC(cudaMalloc(&f->slot_d, 2 * (size_t)f->num_sms * sizeof(double)));
+  CKC(cudaMalloc(&f->slot_k, 2 * (size_t)f->num_sms * sizeof(int)));
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)dd_smem_bytes(kMaxK2)));
+
+  CKC(cudaMemsetAsync(f->sigma, 0, (size_t)f->sigma_elems * sizeof(double), f->stream));
+  CKC(cudaMemsetAsync(f->mu, 0, (size_t)f->n_pad * sizeof(double), f->stream));
+  CKC(cudaMemsetAsync(f->W, 0, panel_bytes, f->stream));
+  CKC(cudaMemsetAsync(f->V, 0, panel_bytes, f->stream));
+  CKC(cudaMemsetAsync(f->Pp, 0, (size_t)f->n_pad * sizeof(double4), f->stream));
+  CKC(cudaMemsetAsync(f->D, 0, (size_t)f->N * sizeof(double4), f->stream));
+  CKC(cudaMemsetAsync(f->cnt, 0, sizeof(int), f->stream));
+  CKC(cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
+  CKC(cudaMemsetAsync(f->prev_xy, 0, 2 * sizeof(double), f->stream));
+  CKC(cudaMemsetAsync(f->bar, 0, sizeof(unsigned long long), f->stream));
+  init_prior_kernel<<<(2 * f->N + 255) / 256, 256, 0, f->stream>>>(f->sigma, f->n_pad, f->n_int, cfg->prior);
+  f->launches++;
+  CKC(cudaGetLastError());
+  if (ensure_io(f, cfg->max_scan > 0 ? cfg->max_scan : 64) != EKF_OK) { ekf_destroy(f); return EKF_ERR_CUDA; }
+  CKC(cudaStreamSynchronize(f->stream));
+#undef CKC
+  *out = f;
+  return EKF_OK;
+}
+
+int ekf_set_stream(ekf_filter *f, void *cuda_stream) {
+  if (!f) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  CK(f, cudaStreamSynchronize(f->stream));
+  f->stream = cuda_stream ? (cudaStream_t)cuda_stream : f->own_stream;
+  return EKF_OK;
+}
+
+int ekf_synchronize(ekf_filter *f) {
+  if (!f) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  CK(f, cudaStreamSynchronize(f->stream));
+  return EKF_OK;
+}
+
+int ekf_last_status(ekf_filter *f) {
+  if (!f) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  CK(f, cudaStreamSynchronize(f->stream));
+  int dev_status = 0;
+  CK(f, cudaMemcpyAsync(&dev_status, f->status, sizeof(int), cudaMemcpyDeviceToHost, f->stream));
+  CK(f, cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
+  CK(f, cudaStreamSynchronize(f->stream));
+  int s = f->latched != EKF_OK ? f->latched : dev_status;
+  f->latched = EKF_OK;
+  return s;
+}
+
+const char *ekf_last_cuda_error(ekf_filter *f) { return f ? f->cuda_err.c_str() : ""; }
+
+int ekf_enable_timing(ekf_filter *f, int32_t on) {
+  if (!f) return EKF_ERR_INVALID;
+  f->timing = on != 0;
+  return EKF_OK;
+}
+
+int ekf_last_timing(ekf_filter *f, float *seq_ms, float *downdate_ms) {
+  if (!f) return EKF_ERR_INVALID;
+  if (f->ev_valid) {
+    DeviceGuard guard(f->device);
+    CK(f, cudaEventSynchronize(f->ev[2]));
+    CK(f, cudaEventElapsedTime(&f->seq_ms, f->ev[0], f->ev[1]));
+    CK(f, cudaEventElapsedTime(&f->dd_ms, f->ev[1], f->ev[2]));
+  }
+  if (seq_ms) *seq_ms = f->seq_ms;
+  if (downdate_ms) *downdate_ms = f->dd_ms;
+  return EKF_OK;
+}
+
+int ekf_launch_count(ekf_filter *f, int64_t *launches) {
+  if (!f || !launches) return EKF_ERR_INVALID;
+  *launches = f->launches;
+  return EKF_OK;
+}
+
+int ekf_sigma_storage(ekf_filter *f, int64_t *stored_doubles, int64_t *n_pad) {
+  if (!f) return EKF_ERR_INVALID;
+  if (stored_doubles) *stored_doubles = f->sigma_elems;
+  if (n_pad) *n_pad = f->n_pad;
+  return EKF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+// Part of ekf_abi.cu: the scan update (prediction + measurement loop + covariance pass).
+
+namespace {
+
+// Launches the sequential kernel for measurements [t0, t0+mc) of a scan and, when mc > 0, the
+// covariance pass for the 2*mc panel columns it produced.  All pointers are device pointers.
+int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, const double *xy_dev,
+                 const int32_t *ids_dev, const uint8_t *action_dev, int32_t *assoc_dev, int finish,
+                 double *pose_out_dev, int *cnt_out_dev) {
+  SeqParams sp{};
+  sp.N = f->N; sp.n_pad = f->n_pad; sp.kmax = f->kmax;
+  sp.q_noise = f->cfg.q_noise; sp.r_noise = f->cfg.r_noise; sp.thr = f->cfg.mah_threshold;
+  sp.sigma = f->sigma; sp.mu = f->mu; sp.Pp = f->Pp; sp.D = f->D; sp.W = f->W; sp.V = f->V;
+  sp.cnt = f->cnt; sp.prev_xy = f->prev_xy; sp.status = f->status;
+  sp.pose = pose_dev; sp.xy = xy_dev; sp.ids = ids_dev; sp.action = action_dev;
+  sp.m = mc; sp.do_predict = do_predict; sp.finish = finish;
+  sp.assoc_out = assoc_dev; sp.pose_out = pose_out_dev; sp.cnt_out = cnt_out_dev;
+  sp.bar = f->bar; sp.bar_base = f->bar_base;
+  sp.slot_d = f->slot_d; sp.slot_k = f->slot_k;
+  f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
+
+  if (f->timing) CK(f, cudaEventRecord(f->ev[0], f->stream));
+  void *args[] = {(void *)&sp};
+  CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel, dim3(f->seq_grid), dim3(kSeqThreads), args, 0,
+                                    f->stream));
+  f->launches++;
+  if (f->timing) CK(f, cudaEventRecord(f->ev[1], f->stream));
+  if (mc > 0) {
+    DdParams dp{};
+    dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
+    dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = 2 * mc;
+    dp.row_begin = 0; dp.row_end = f->n_pad;
+    dp.total_chunks = dd_total_chunks(f->n_pad, 0, f->n_pad);
+    long long grid = f->dd_grid;
+    if (grid > dp.total_chunks) grid = dp.total_chunks;
+    ekf_downdate_kernel<<<(unsigned)grid, kDdThreads, dd_smem_bytes(dp.k2), f->stream>>>(dp);
+    f->launches++;
+    CK(f, cudaGetLastError());
+  }
+  if (f->timing) { CK(f, cudaEventRecord(f->ev[2], f->stream)); f->ev_valid = true; }
+  return EKF_OK;
+}
+
+// One whole scan from device inputs; splits into chunks of kMaxChunkM measurements.
+int scan_device(ekf_filter *f, const double *pose_dev, int m, const double *xy_dev, const int32_t *ids_dev,
+                const uint8_t *action_dev, int32_t *assoc_dev, double *pose_out_dev, int *cnt_out_dev) {
+  int t0 = 0;
+  bool first = true;
+  do {
+    const int mc = (m - t0) < kMaxChunkM ? (m - t0) : kMaxChunkM;
+    const int last = (t0 + mc >= m);
+    int rc = launch_chunk(f, pose_dev, first && pose_dev != nullptr, mc, xy_dev ? xy_dev + 2 * t0 : nullptr,
+                          ids_dev ? ids_dev + t0 : nullptr, action_dev ? action_dev + t0 : nullptr,
+                          assoc_dev ? assoc_dev + t0 : nullptr, last && m > 0, pose_out_dev, cnt_out_dev);
+    if (rc != EKF_OK) return rc;
+    first = false;
+    t0 += mc;
+  } while (t0 < m);
+  return EKF_OK;
+}
+
+// Host-pointer scan: pack inputs into pinned staging, one H2D, kernels, one D2H, sync.
+int scan_host(ekf_filter *f, const double *pose, int m, const double *xy, const int32_t *ids, const uint8_t *action,
+              int32_t *out_assoc, int32_t *out_count, double *out_pose) {
+  int rc = ensure_io(f, m);
+  if (rc != EKF_OK) return rc;
+  const IoLayout in(m);
+  const ResLayout res(m);
+  if (pose) memcpy(f->io_host + in.pose, pose, 24);
+  if (m > 0) {
+    memcpy(f->io_host + in.xy, xy, (size_t)16 * m);
+    if (ids) memcpy(f->io_host + in.ids, ids, (size_t)4 * m);
+    if (action) memcpy(f->io_host + in.action, action, (size_t)m);
+  }
+  CK(f, cudaMemcpyAsync(f->io_dev, f->io_host, in.total, cudaMemcpyHostToDevice, f->stream));
+  rc = scan_device(f, pose ? reinterpret_cast<const double *>(f->io_dev + in.pose) : nullptr, m,
+                   reinterpret_cast<const double *>(f->io_dev + in.xy),
+                   ids ? reinterpret_cast<const int32_t *>(f->io_dev + in.ids) : nullptr,
+                   action ? reinterpret_cast<const uint8_t *>(f->io_dev + in.action) : nullptr,
+                   reinterpret_cast<int32_t *>(f->res_dev + res.assoc), reinterpret_cast<double *>(f->res_dev + res.pose),
+                   reinterpret_cast<int *>(f->res_dev + res.cnt));
+  if (rc != EKF_OK) return rc;
+  CK(f, cudaMemcpyAsync(f->res_dev + res.status, f->status, sizeof(int), cudaMemcpyDeviceToDevice, f->stream));
+  CK(f, cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
+  CK(f, cudaMemcpyAsync(f->res_host, f->res_dev, res.total, cudaMemcpyDeviceToHost, f->stream));
+  CK(f, cudaStreamSynchronize(f->stream));
+  if (out_assoc && m > 0) memcpy(out_assoc, f->res_host + res.assoc, (size_t)4 * m);
+  if (out_count) memcpy(out_count, f->res_host + res.cnt, 4);
+  if (out_pose) memcpy(out_pose, f->res_host + res.pose, 24);
+  int dev_status = 0;
+  memcpy(&dev_status, f->res_host + res.status, 4);
+  return dev_status;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ekf_predict(ekf_filter *f, double theta, double x, double y) {
+  if (!f) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  const double pose[3] = {theta, x, y};
+  return scan_host(f, pose, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+}
+
+int ekf_update_known(ekf_filter *f, int32_t m, const int32_t *ids, const double *xy, const uint8_t *action) {
+  if (!f || m < 0) return EKF_ERR_INVALID;
+  if (m == 0) return EKF_ERR_EMPTY_SCAN;
+  if (!ids || !xy) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  return scan_host(f, nullptr, m, xy, ids, action, nullptr, nullptr, nullptr);
+}
+
+int ekf_update_unknown(ekf_filter *f, int32_t m, const double *xy, int32_t *out_assoc, int32_t *out_count) {
+  if (!f || m < 0) return EKF_ERR_INVALID;
+  if (m == 0) return EKF_ERR_EMPTY_SCAN;
+  if (!xy) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  return scan_host(f, nullptr, m, xy, nullptr, nullptr, out_assoc, out_count, nullptr);
+}
+
+int ekf_scan(ekf_filter *f, const double pose[3], int32_t m, const double *xy, const int32_t *ids,
+             const uint8_t *action, int32_t *out_assoc, int32_t *out_count, double out_pose[3]) {
+  if (!f || m < 0 || !pose) return EKF_ERR_INVALID;
+  if (m == 0) return EKF_ERR_EMPTY_SCAN;
+  if (!xy) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  return scan_host(f, pose, m, xy, ids, action, out_assoc, out_count, out_pose);
+}
+
+int ekf_scan_dev(ekf_filter *f, const double *pose_dev, int32_t m, const double *xy_dev, const int32_t *ids_dev,
+                 const uint8_t *action_dev, int32_t *assoc_dev) {
+  if (!f || m < 0 || !pose_dev) return EKF_ERR_INVALID;
+  if (m == 0) return EKF_ERR_EMPTY_SCAN;
+  if (!xy_dev) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  int rc = ensure_io(f, 1);
+  if (rc != EKF_OK) return rc;
+  const ResLayout res(1);
+  return scan_device(f, pose_dev, m, xy_dev, ids_dev, action_dev, assoc_dev,
+                     reinterpret_cast<double *>(f->res_dev + res.pose), reinterpret_cast<int *>(f->res_dev + res.cnt));
+}
+
+}  // extern "C"

@@ -1,0 +1,147 @@
+/* ekf_slam_b200.h - C ABI of the B200-native EKF-SLAM core.
+ *
+ * The reference (maxipalay/ekf-slam) has no plugin / FFI boundary for its filter: the whole
+ * EKF is written inline in two ROS callbacks of class Slam.  This ABI is the seam
+ * SURVEY.md section 8(b) makes explicit - it replaces
+ *     nuslam/src/slam.cpp:127-139,659-676   filter members and their initialisation
+ *     nuslam/src/slam.cpp:186-198 / 323-335 pose injection + prediction
+ *     nuslam/src/slam.cpp:201-271           known-association measurement loop
+ *     nuslam/src/slam.cpp:338-489           unknown-association (Mahalanobis) loop
+ * and leaves the node shell (tf, markers, odometry; slam.cpp:273-316, 490-530, 575-634) as
+ * the caller.  INTEGRATION.md shows the edit a maintainer would make in slam.cpp.
+ *
+ * Conventions
+ *   - every function returns an ekf_status (0 = OK); nothing throws across the boundary;
+ *   - plain pointers and sizes only; "host" pointers are caller-owned host memory,
+ *     "device" pointers (suffix _dev) are caller-owned device memory on the filter's GPU;
+ *   - state vectors use the reference's layout [theta, x, y, m1x, m1y, ...] (slam.cpp:186-188,
+ *     214-215), n = 3 + 2N; Sigma blocks are row-major n x n blocks of the symmetric matrix;
+ *   - one caller thread per handle (the reference's executor is single-threaded,
+ *     slam.cpp:680-686); host-pointer calls are synchronous at return, *_dev calls are
+ *     stream-ordered and asynchronous (errors latch in the handle, see ekf_last_status);
+ *   - there is NO CPU fallback: every entry point needs a CUDA device and fails with
+ *     EKF_ERR_CUDA / EKF_ERR_NO_DEVICE otherwise.
+ */
+#ifndef EKF_SLAM_B200_H
+#define EKF_SLAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum ekf_status {
+  EKF_OK = 0,
+  EKF_ERR_INVALID = 1,    /* bad argument (null pointer, negative size, unknown option) */
+  EKF_ERR_CAPACITY = 2,   /* a new landmark was needed but counter_obstacles == N
+                             (the reference indexes out of bounds here: slam.cpp:351 with :665) */
+  EKF_ERR_EMPTY_SCAN = 3, /* m == 0 (the reference throws at msg.markers.at(0): slam.cpp:281,498) */
+  EKF_ERR_BAD_ID = 4,     /* known-association id outside [0, N) (Armadillo bounds error) */
+  EKF_ERR_CUDA = 5,       /* a CUDA call failed; see ekf_last_cuda_error */
+  EKF_ERR_NO_DEVICE = 6,  /* no usable sm_100 device */
+  EKF_ERR_NOMEM = 7
+} ekf_status;
+
+/* Filter constants.  Defaults (ekf_default_config) are the reference's hard-coded members:
+ * n_landmarks{50}, q_noise{1e-2}, r_noise{1e-2}, mah_threshold = 2.0 (slam.cpp:665-671) and the
+ * 10e6 landmark prior (slam.cpp:130). */
+typedef struct ekf_config {
+  int32_t n_landmarks;   /* N: landmark capacity; n = 3 + 2N */
+  double q_noise;        /* Qbar = diag(q,q,q,0,...)        slam.cpp:135-136 */
+  double r_noise;        /* R = r * I2                      slam.cpp:139 */
+  double mah_threshold;  /* new-landmark threshold          slam.cpp:671,406-408 */
+  double prior;          /* initial landmark variance       slam.cpp:130 */
+  int32_t device;        /* CUDA device ordinal, -1 = current device */
+  int32_t max_scan;      /* hint: largest m per call (0 = 64); larger scans still work */
+  /* row sharding of one large map over several GPUs (one process per GPU): this handle owns
+   * the covariance rows of shard `shard_rank` out of `shard_count` (equal-area split).
+   * shard_count <= 1 means a whole, unsharded filter. */
+  int32_t shard_rank;
+  int32_t shard_count;
+} ekf_config;
+
+typedef struct ekf_filter ekf_filter;       /* one EKF (slam.cpp:659-676) */
+typedef struct ekf_batch ekf_batch;         /* B independent small EKFs, one CTA each */
+
+void ekf_default_config(ekf_config *cfg);
+const char *ekf_status_string(int status);
+const char *ekf_version(void);
+
+/* ---- lifetime: replaces slam.cpp:127-139 ------------------------------------------------ */
+int ekf_create(const ekf_config *cfg, ekf_filter **out);
+int ekf_destroy(ekf_filter *f);
+/* run the handle's kernels on a caller stream (a cudaStream_t cast to void*; NULL = the
+ * handle's own stream).  Lets a harness time the work with events on that stream. */
+int ekf_set_stream(ekf_filter *f, void *cuda_stream);
+int ekf_synchronize(ekf_filter *f);
+/* latched status of asynchronous work since the last call of this function (syncs) */
+int ekf_last_status(ekf_filter *f);
+const char *ekf_last_cuda_error(ekf_filter *f);
+
+/* ---- the scan update -------------------------------------------------------------------- */
+/* slam.cpp:184-198: `pose` is the already composed t_map_odom * t_odom_robot as (theta, x, y)
+ * (raw theta; it is wrapped inside like slam.cpp:186).  Overwrites state[0..2], then
+ * Sigma <- A Sigma A^T + Qbar with dx, dy taken against the pose the filter held at the end of
+ * the previous update (filter_previous_configuration, slam.cpp:190-191,291). */
+int ekf_predict(ekf_filter *f, double theta, double x, double y);
+
+/* slam.cpp:201-271: m sightings with known landmark ids.  xy = body-frame (x, y) pairs
+ * (marker.pose.position), action may be NULL; entries equal to 2 (Marker::DELETE) are skipped
+ * (slam.cpp:205).  A landmark whose two state slots are exactly 0.0 is initialised from the
+ * sighting first (slam.cpp:213-216). */
+int ekf_update_known(ekf_filter *f, int32_t m, const int32_t *ids, const double *xy,
+                     const uint8_t *action);
+
+/* slam.cpp:338-489: m sightings, Mahalanobis association, processed sequentially (measurement
+ * i+1 sees the state and Sigma left by measurement i).  out_assoc[i] = landmark index the
+ * sighting was fused with (the value of min_index at slam.cpp:443; a new landmark gets the old
+ * counter_obstacles).  out_count = counter_obstacles afterwards.  Either may be NULL. */
+int ekf_update_unknown(ekf_filter *f, int32_t m, const double *xy, int32_t *out_assoc,
+                       int32_t *out_count);
+
+/* predict + update in one call (what each sensor callback does), inputs and outputs in DEVICE
+ * memory, asynchronous: pose_dev[3], xy_dev[2m], ids_dev[m] (known) / NULL (unknown),
+ * action_dev[m] or NULL, assoc_dev[m] or NULL.  Used by the throughput harness; errors latch. */
+int ekf_scan_dev(ekf_filter *f, const double *pose_dev, int32_t m, const double *xy_dev,
+                 const int32_t *ids_dev, const uint8_t *action_dev, int32_t *assoc_dev);
+/* the same with HOST buffers (copies in, runs, copies assoc / count / pose back, syncs) */
+int ekf_scan(ekf_filter *f, const double pose[3], int32_t m, const double *xy, const int32_t *ids,
+             const uint8_t *action, int32_t *out_assoc, int32_t *out_count, double out_pose[3]);
+
+/* ---- accessors (slam.cpp:273-274, 304-306, 518-520) ------------------------------------- */
+int ekf_state_dim(ekf_filter *f, int32_t *n);                 /* n = 3 + 2N */
+int ekf_get_pose(ekf_filter *f, double out[3]);               /* theta, x, y */
+int ekf_get_state(ekf_filter *f, double *out, int32_t n);     /* first n entries of the state */
+int ekf_get_count(ekf_filter *f, int32_t *count);             /* counter_obstacles */
+int ekf_get_landmarks(ekf_filter *f, double *out_xy, int32_t max_landmarks, int32_t *count);
+/* rows [i0,i1) x cols [j0,j1) of the symmetric Sigma, row-major into out (leading dim j1-j0) */
+int ekf_get_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32_t j1, double *out);
+
+/* ---- fixtures: checkpoint / restore, test set-up ------------------------------------------ */
+int ekf_set_state(ekf_filter *f, const double *in, int32_t n);
+int ekf_set_count(ekf_filter *f, int32_t count);
+int ekf_set_previous_xy(ekf_filter *f, double x, double y);   /* filter_previous_configuration */
+int ekf_get_previous_xy(ekf_filter *f, double out[2]);
+/* writes the entries with row >= col of the given block into the stored triangle */
+int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32_t j1, const double *in);
+/* Procedural large-map fixture: `count` landmarks on a jittered
+ * unit grid of `grid_w` columns, state consistent with it, Sigma = block-diagonal SPD + a
+ * rank-8 hash-generated cross term.  Deterministic in `seed`; generated on the device. */
+int ekf_fill_procedural(ekf_filter *f, uint64_t seed, int32_t count, int32_t grid_w);
+
+/* ---- measured facts for the harness -------------------------------------------------------- */
+/* bytes the covariance pass streams per scan (stored triangle, read + write) and the stored
+ * element count; used for the roofline arithmetic in bench.py / DESIGN.md */
+int ekf_sigma_storage(ekf_filter *f, int64_t *stored_doubles, int64_t *n_pad);
+/* number of kernels this handle has launched since creation */
+int ekf_launch_count(ekf_filter *f, int64_t *launches);
+/* device-time of the last `ekf_scan*` call's covariance pass and sequential phase, ms
+ * (CUDA events on the handle's stream; valid after ekf_synchronize). */
+int ekf_last_timing(ekf_filter *f, float *seq_ms, float *downdate_ms);
+int ekf_enable_timing(ekf_filter *f, int32_t on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
