@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py - the EKF-SLAM hot path on B200: scan-updates/s at N = 10,000 landmarks.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--landmarks N] [--m M]
+
+One "step" = one scan update of ONE filter: pose injection + prediction + m x (Mahalanobis
+association, gain, state update) + the fused covariance pass (BASELINE.json metric; config
+"single large map N=10,000 landmarks (n=20,003), 20 measurements/scan").  Prints ONE JSON line
+(contract in the task statement): `value` = scans/s with inputs resident in HBM, `e2e` = the same
+through the host-buffer C ABI call (H2D + D2H inside), `roofline` for the dominant kernel
+(ekf_downdate_kernel, HBM-bound), `cpu_baseline` = oracle B ("port") on the host cores.
+
+N > 1 GPUs (round 1): independent replicas, one filter per GPU, no collective on the data path
+("weak" scaling); the row-sharded single map is DESIGN.md section "multi-GPU" (next).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "ekf_scan_updates_per_s_N10k"
+UNIT = "scan-updates/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--landmarks", type=int, default=10000)
+    ap.add_argument("--m", type=int, default=20)
+    ap.add_argument("--seed", type=int, default=7)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-meas", type=int, default=2,
+                    help="measurements of one scan the CPU baseline actually runs (scaled to m)")
+    return ap.parse_args()
+
+
+def peaks():
+    """measured roofline denominators written by the driver, else the recipe's fallback"""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.dev = device_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.dev), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons, power = [], None, set(), []
+        for (t, line) in self.rows:
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 8:
+                continue
+            try:
+                if t0 <= t <= t1 + 0.12:
+                    sm.append(float(parts[1])); power.append(float(parts[3]))
+                smax = float(parts[2])
+            except ValueError:
+                continue
+            if t0 <= t <= t1 + 0.12:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                                   parts[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
+                "power_w": float(np.median(power)) if power else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def make_workload(state0, count, m, n_scans, seed):
+    """Per-scan poses and sightings for the large-map config: the robot circles in the middle of
+    the landmark grid; each scan sights the m nearest landmarks (body frame, sigma = 1e-3 per
+    axis like nusim's fake sensor, nusim.cpp:88,202,339-340)."""
+    rng = np.random.default_rng(seed)
+    lm = state0[3:3 + 2 * count].reshape(-1, 2)
+    side = np.sqrt(count)
+    cx = cy = side / 2.0
+    rad = max(1.5, side / 5.0)
+    poses = np.zeros((n_scans, 3))
+    xy = np.zeros((n_scans, m, 2))
+    ids = np.zeros((n_scans, m), dtype=np.int32)
+    for s in range(n_scans):
+        ang = 0.004 * s
+        x, y = cx + rad * np.cos(ang), cy + rad * np.sin(ang)
+        th = ang + np.pi / 2
+        d = np.hypot(lm[:, 0] - x, lm[:, 1] - y)
+        near = np.argpartition(d, m)[:m]
+        rng.shuffle(near)
+        c, sn = np.cos(th), np.sin(th)
+        dx, dy = lm[near, 0] - x, lm[near, 1] - y
+        xy[s] = np.stack([c * dx + sn * dy, -sn * dx + c * dy], axis=1) + rng.normal(0, 1e-3, (m, 2))
+        ids[s] = near
+        poses[s] = (th, x, y)
+    return poses, xy, ids
+
+
+def algorithmic_bytes(n, m):
+    """B_scan = 8 n (n+1) + 8 n 9 m; the covariance pass alone = 8 n (n+1)."""
+    return 8.0 * n * (n + 1) + 8.0 * n * 9 * m, 8.0 * n * (n + 1)
+
+
+def cpu_setup(N, count, seed, state0=None, sigma_rows=None):
+    """Oracle B (oracle/ekf_struct.c) holding the large map: either a copy of the GPU filter's
+    state / Sigma, or a CPU-generated map of the same structure (block-diagonal SPD + rank-8)."""
+    import struct_oracle as so
+    L = so.lib()
+    L.ekfo_num_threads.restype = int
+    cores = int(L.ekfo_num_threads())
+    o = so.StructEkf(n_landmarks=N)
+    n = o.n
+    if state0 is None:
+        rng = np.random.default_rng(seed)
+        side = int(np.ceil(np.sqrt(count)))
+        k = np.arange(count)
+        lm = np.stack([k % side + rng.uniform(-0.2, 0.2, count), k // side + rng.uniform(-0.2, 0.2, count)], 1)
+        o.state[3:3 + 2 * count] = lm.reshape(-1)
+        U = 0.01 * rng.uniform(-1, 1, (n, 8))
+        blk = 4096
+        for i0 in range(0, n, blk):
+            o.sigma[i0:i0 + blk, :] = U[i0:i0 + blk] @ U.T
+        idx = np.arange(n)
+        o.sigma[idx, idx] += 1e-3 * rng.uniform(1.0, 2.0, n)
+    else:
+        o.state[:] = state0
+        sigma_rows(o.sigma)
+    o.count = count
+    return o, cores
+
+
+def cpu_step(o, pose, xy_scan, m, sample_meas):
+    """One bounded sample of a scan: prediction + the first `sample_meas` measurements, the
+    measurement part scaled to m.  Returns the seconds a whole scan would take."""
+    t0 = time.perf_counter()
+    o.predict(*pose)
+    t1 = time.perf_counter()
+    o.update_unknown(xy_scan[:sample_meas])
+    t2 = time.perf_counter()
+    return (t1 - t0) + (t2 - t1) * m / sample_meas
+
+
+def cpu_desc(N, m, sample_meas, steps):
+    return (f"oracle B (oracle/ekf_struct.c: structured O(n^2)-per-measurement restatement of "
+            f"slam.cpp:321-489, pthreads on all host cores) at N={N}: per step, prediction + {sample_meas} of "
+            f"{m} measurements of a scan are run and the measurement part is scaled x{m}/{sample_meas}; {steps} step(s)")
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port; slam.cpp itself needs
+    Armadillo + ROS 2 and cannot be built here) on the host cores, same config and metric."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    N, m = args.landmarks, args.m
+    o, cores = cpu_setup(N, N, args.seed)
+    total = args.warmup + args.steps
+    poses, xy, _ = make_workload(np.array(o.state), N, m, total, args.seed + 1)
+    o.set_prev(poses[0][1], poses[0][2])
+    secs = [cpu_step(o, poses[i], xy[i], m, args.cpu_sample_meas) for i in range(total)][args.warmup:]
+    o.close()
+    value = float(len(secs) / sum(secs))
+    desc = cpu_desc(N, m, args.cpu_sample_meas, args.steps)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / value, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"single large map N={N} landmarks (n={3 + 2 * N}), {m} measurements/scan, "
+                                   "unknown association, all landmarks mapped (BASELINE.json configs[3])",
+                       "landmarks": N, "m": m},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import ekf_slam_b200 as ekf
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the product has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    N, m, K, W = args.landmarks, args.m, args.steps, args.warmup
+    n = 3 + 2 * N
+    f = ekf.EkfSlam(n_landmarks=N, device=local, max_scan=m)
+    side = int(np.ceil(np.sqrt(N)))
+    f.fill_procedural(args.seed + rank, N, side)
+    state0 = f.state()
+    n_scans = 2 * (W + K)
+    poses, xy, ids = make_workload(state0, N, m, n_scans, args.seed + 100 + rank)
+    f.set_previous_xy(poses[0][1], poses[0][2])
+    # a non-default stream: the legacy default stream's handle is NULL, which ekf_set_stream reads
+    # as "use the handle's own stream" - the timing events must sit on the stream the kernels use
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    f.set_stream(stream.cuda_stream)
+    d_pose = torch.from_numpy(poses).cuda()
+    d_xy = torch.from_numpy(xy).cuda()
+    d_assoc = torch.full((n_scans, m), -9, dtype=torch.int32, device="cuda")
+    stored, n_pad = f.storage()
+
+    def scan_dev(s):
+        f.scan_dev(d_pose[s].data_ptr(), m, d_xy[s].data_ptr(), 0, 0, d_assoc[s].data_ptr())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) -------------------------------------------------
+    for s in range(W):
+        scan_dev(s)
+    f.enable_timing(K)
+    l0 = f.launch_count()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for s in range(W, W + K):
+        scan_dev(s)
+    e1.record(stream)
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1)
+    ms_total = e0.elapsed_time(e1)
+    launches = f.launch_count() - l0
+    seq_ms, dd_ms = f.read_timing(K)
+    f.enable_timing(0)
+    status = f.last_status()
+
+    # ---- end to end through the host-buffer ABI call (`e2e`) -----------------------------------
+    e_assoc = []
+    barrier()
+    t2 = time.perf_counter()
+    for s in range(W + K, W + 2 * K):
+        a, cnt, _ = f.scan(poses[s], xy[s])
+        e_assoc.append(a)
+    barrier()
+    t3 = time.perf_counter()
+    e2e_s = t3 - t2
+
+    tt = torch.tensor([ms_total, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = float(tt[0]), float(tt[1])
+    assoc_dev = d_assoc[W:W + K].cpu().numpy()
+    assoc_ok = bool((assoc_dev == ids[W:W + K]).all() and
+                    all((np.asarray(a) == ids[W + K + i]).all() for i, a in enumerate(e_assoc)) and status == 0)
+    ok = torch.tensor([1 if assoc_ok else 0], device="cuda")
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if rank != 0:
+        f.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = world * K / (ms_total / 1000.0)
+    e2e_value = world * K / (e2e_ms / 1000.0)
+    b_scan, b_pass = algorithmic_bytes(n, m)
+    peak, peak_src = peaks()
+    dd_avg_ms = float(np.mean(dd_ms)) if len(dd_ms) else float("nan")
+    achieved = b_pass / (dd_avg_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"single large map N={N} landmarks (n={n}), {m} measurements/scan, unknown "
+                               "association, all landmarks mapped (BASELINE.json configs[3])",
+                   "landmarks": N, "m": m, "parallelism": "1 filter per GPU (replicas)" if world > 1 else "1 GPU",
+                   "l2": f"inputs larger than L2: Sigma triangle = {stored * 8 / 1e9:.2f} GB streamed per scan",
+                   "association_bit_exact_vs_expected_ids": bool(ok.item())},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 + 16 * m, "d2h_bytes_per_step": 32 + 4 * m,
+                "ms_per_step": e2e_ms / K},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "ekf_downdate_kernel", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": b_pass, "avg_launch_ms": dd_avg_ms,
+                     "seq_phase_avg_ms": float(np.mean(seq_ms)) if len(seq_ms) else None,
+                     "scan_frac_of_hbm_roofline": (b_scan * value / world / 1e9) / peak},
+    }
+    if not args.no_cpu_baseline:
+        def fill_rows(sig):
+            rows = 2048
+            for i0 in range(0, n, rows):
+                i1 = min(n, i0 + rows)
+                sig[i0:i1, :] = f.sigma_block(i0, i1, 0, n)
+        o, cores = cpu_setup(N, N, args.seed, state0=f.state(), sigma_rows=fill_rows)
+        s0 = W + 2 * K - 1
+        o.set_prev(*f.previous_xy())
+        secs = cpu_step(o, poses[s0], xy[s0], m, args.cpu_sample_meas)
+        o.close()
+        line["cpu_baseline"] = {"value": 1.0 / secs, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": cpu_desc(N, m, args.cpu_sample_meas, 1)}
+    f.close()
+    if world > 1:
+        dist.destroy_process_group()
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -89,7 +89,7 @@ def load() -> C.CDLL:
         "ekf_fill_procedural": (C.c_int, [vp, C.c_uint64, i32, i32]),
         "ekf_sigma_storage": (C.c_int, [vp, i64p, i64p]),
         "ekf_launch_count": (C.c_int, [vp, i64p]),
-        "ekf_last_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+        "ekf_read_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),
         "ekf_enable_timing": (C.c_int, [vp, i32]),
     }
     for name, (res, args) in sigs.items():
@@ -281,10 +281,15 @@ class EkfSlam:
         self._check(self._L.ekf_launch_count(self._h, C.byref(a)), "ekf_launch_count")
         return int(a.value)
 
-    def enable_timing(self, on: bool = True):
-        self._check(self._L.ekf_enable_timing(self._h, int(on)), "ekf_enable_timing")
+    def enable_timing(self, ring_scans: int):
+        self._check(self._L.ekf_enable_timing(self._h, int(ring_scans)), "ekf_enable_timing")
 
-    def last_timing(self):
-        a, b = C.c_float(0), C.c_float(0)
-        self._check(self._L.ekf_last_timing(self._h, C.byref(a), C.byref(b)), "ekf_last_timing")
-        return float(a.value), float(b.value)
+    def read_timing(self, max_scans: int):
+        """(seq_ms[], downdate_ms[]) of the most recent scans, oldest first (synchronises)."""
+        a = np.zeros(max_scans, dtype=np.float32)
+        b = np.zeros(max_scans, dtype=np.float32)
+        n = C.c_int32(0)
+        fp = C.POINTER(C.c_float)
+        self._check(self._L.ekf_read_timing(self._h, a.ctypes.data_as(fp), b.ctypes.data_as(fp), max_scans,
+                                            C.byref(n)), "ekf_read_timing")
+        return a[:n.value].astype(np.float64), b[:n.value].astype(np.float64)

@@ -9,6 +9,7 @@
 
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/ekf_slam_b200.h"
 #include "ekf_downdate.cuh"
@@ -41,10 +42,10 @@ struct ekf_filter {
   size_t scratch_cap = 0;
   // streams / events / bookkeeping
   cudaStream_t own_stream = nullptr, stream = nullptr;
-  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
-  bool timing = false;
-  bool ev_valid = false;
-  float seq_ms = 0.f, dd_ms = 0.f;
+  // optional per-scan timing: a ring of (start, after sequential phase, after covariance pass) events
+  std::vector<cudaEvent_t> ev;
+  int ev_cap = 0;          // scans the ring holds; 0 = timing off
+  int64_t ev_count = 0;    // scans recorded since timing was enabled
   int64_t launches = 0;
   int seq_grid = 1;
   int dd_grid = 1;

@@ -44,6 +44,7 @@ int ekf_destroy(ekf_filter *f) {
     if (f->io_host) cudaFreeHost(f->io_host);
     if (f->res_host) cudaFreeHost(f->res_host);
     for (auto &e : f->ev) if (e) cudaEventDestroy(e);
+    f->ev.clear();
     if (f->own_stream) cudaStreamDestroy(f->own_stream);
   }
   delete f;
@@ -85,7 +86,6 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
 
   CKC(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
   f->stream = f->own_stream;
-  for (auto &e : f->ev) CKC(cudaEventCreate(&e));
   const size_t panel_bytes = (size_t)f->n_pad * f->kmax * sizeof(double);
   CKC(cudaMalloc(&f->sigma, (size_t)f->sigma_elems * sizeof(double)));
   CKC(cudaMalloc(&f->mu, (size_t)f->n_pad * sizeof(double)));
@@ -161,22 +161,35 @@ int ekf_last_status(ekf_filter *f) {
 
 const char *ekf_last_cuda_error(ekf_filter *f) { return f ? f->cuda_err.c_str() : ""; }
 
-int ekf_enable_timing(ekf_filter *f, int32_t on) {
-  if (!f) return EKF_ERR_INVALID;
-  f->timing = on != 0;
+int ekf_enable_timing(ekf_filter *f, int32_t ring_scans) {
+  if (!f || ring_scans < 0) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  CK(f, cudaStreamSynchronize(f->stream));
+  for (auto &e : f->ev) if (e) cudaEventDestroy(e);
+  f->ev.assign((size_t)ring_scans * 3, nullptr);
+  for (auto &e : f->ev) CK(f, cudaEventCreate(&e));
+  f->ev_cap = ring_scans;
+  f->ev_count = 0;
   return EKF_OK;
 }
 
-int ekf_last_timing(ekf_filter *f, float *seq_ms, float *downdate_ms) {
-  if (!f) return EKF_ERR_INVALID;
-  if (f->ev_valid) {
-    DeviceGuard guard(f->device);
-    CK(f, cudaEventSynchronize(f->ev[2]));
-    CK(f, cudaEventElapsedTime(&f->seq_ms, f->ev[0], f->ev[1]));
-    CK(f, cudaEventElapsedTime(&f->dd_ms, f->ev[1], f->ev[2]));
+int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t max_scans, int32_t *n_scans) {
+  if (!f || max_scans < 0) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  CK(f, cudaStreamSynchronize(f->stream));
+  int64_t have = f->ev_count < f->ev_cap ? f->ev_count : f->ev_cap;
+  if (have > max_scans) have = max_scans;
+  // the most recent `have` scans, oldest first
+  for (int64_t i = 0; i < have; ++i) {
+    const int64_t scan = f->ev_count - have + i;
+    const size_t slot = (size_t)(scan % f->ev_cap) * 3;
+    float a = 0.f, b = 0.f;
+    CK(f, cudaEventElapsedTime(&a, f->ev[slot], f->ev[slot + 1]));
+    CK(f, cudaEventElapsedTime(&b, f->ev[slot + 1], f->ev[slot + 2]));
+    if (seq_ms) seq_ms[i] = a;
+    if (downdate_ms) downdate_ms[i] = b;
   }
-  if (seq_ms) *seq_ms = f->seq_ms;
-  if (downdate_ms) *downdate_ms = f->dd_ms;
+  if (n_scans) *n_scans = (int32_t)have;
   return EKF_OK;
 }
 

@@ -19,12 +19,14 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k;
   f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
 
-  if (f->timing) CK(f, cudaEventRecord(f->ev[0], f->stream));
+  const bool timed = f->ev_cap > 0 && mc > 0;
+  const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 3 : 0;
+  if (timed) CK(f, cudaEventRecord(f->ev[slot], f->stream));
   void *args[] = {(void *)&sp};
   CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel, dim3(f->seq_grid), dim3(kSeqThreads), args, 0,
                                     f->stream));
   f->launches++;
-  if (f->timing) CK(f, cudaEventRecord(f->ev[1], f->stream));
+  if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
   if (mc > 0) {
     DdParams dp{};
     dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
@@ -37,7 +39,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
     f->launches++;
     CK(f, cudaGetLastError());
   }
-  if (f->timing) { CK(f, cudaEventRecord(f->ev[2], f->stream)); f->ev_valid = true; }
+  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); f->ev_count++; }
   return EKF_OK;
 }
 

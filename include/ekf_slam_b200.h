@@ -136,10 +136,12 @@ int ekf_fill_procedural(ekf_filter *f, uint64_t seed, int32_t count, int32_t gri
 int ekf_sigma_storage(ekf_filter *f, int64_t *stored_doubles, int64_t *n_pad);
 /* number of kernels this handle has launched since creation */
 int ekf_launch_count(ekf_filter *f, int64_t *launches);
-/* device-time of the last `ekf_scan*` call's covariance pass and sequential phase, ms
- * (CUDA events on the handle's stream; valid after ekf_synchronize). */
-int ekf_last_timing(ekf_filter *f, float *seq_ms, float *downdate_ms);
-int ekf_enable_timing(ekf_filter *f, int32_t on);
+/* Per-scan device timing with CUDA events on the handle's stream.  ekf_enable_timing(f, r)
+ * keeps the last r scans (r = 0 switches it off); ekf_read_timing synchronises and returns, for
+ * the most recent scans (oldest first), the milliseconds of the sequential phase and of the
+ * covariance pass.  A scan split into several passes (m > 24) counts once per pass. */
+int ekf_enable_timing(ekf_filter *f, int32_t ring_scans);
+int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t max_scans, int32_t *n_scans);
 
 #ifdef __cplusplus
 }
