@@ -32,7 +32,7 @@ struct ekf_filter {
   double *prev_xy = nullptr;
   unsigned long long *bar = nullptr;
   unsigned long long bar_base = 0;
-  double *slot_d = nullptr;
+  double *slot_d = nullptr, *slot_rec = nullptr;
   int *slot_k = nullptr;
   // staging for the host-pointer entry points
   unsigned char *io_dev = nullptr, *io_host = nullptr;   // inputs: pose | xy | ids | action

@@ -39,7 +39,7 @@ int ekf_destroy(ekf_filter *f) {
     if (f->stream) cudaStreamSynchronize(f->stream);
     cudaFree(f->sigma); cudaFree(f->mu); cudaFree(f->W); cudaFree(f->V);
     cudaFree(f->Pp); cudaFree(f->D); cudaFree(f->cnt); cudaFree(f->status);
-    cudaFree(f->prev_xy); cudaFree(f->bar); cudaFree(f->slot_d); cudaFree(f->slot_k);
+    cudaFree(f->prev_xy); cudaFree(f->bar); cudaFree(f->slot_d); cudaFree(f->slot_k); cudaFree(f->slot_rec);
     cudaFree(f->io_dev); cudaFree(f->res_dev); cudaFree(f->scratch_dev);
     if (f->io_host) cudaFreeHost(f->io_host);
     if (f->res_host) cudaFreeHost(f->res_host);
@@ -108,6 +108,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   if (f->dd_grid < 1) f->dd_grid = 1;
   CKC(cudaMalloc(&f->slot_d, 2 * (size_t)f->num_sms * sizeof(double)));
   CKC(cudaMalloc(&f->slot_k, 2 * (size_t)f->num_sms * sizeof(int)));
+  CKC(cudaMalloc(&f->slot_rec, 2 * (size_t)f->num_sms * kRecStride * sizeof(double)));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(kMaxK2)));
 

@@ -16,7 +16,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   sp.m = mc; sp.do_predict = do_predict; sp.finish = finish;
   sp.assoc_out = assoc_dev; sp.pose_out = pose_out_dev; sp.cnt_out = cnt_out_dev;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
-  sp.slot_d = f->slot_d; sp.slot_k = f->slot_k;
+  sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
   f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
 
   const bool timed = f->ev_cap > 0 && mc > 0;
@@ -30,7 +30,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   if (mc > 0) {
     DdParams dp{};
     dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
-    dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = 2 * mc;
+    dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;  // whole k-steps; pad columns are zero
     dp.row_begin = 0; dp.row_end = f->n_pad;
     dp.total_chunks = dd_total_chunks(f->n_pad, 0, f->n_pad);
     long long grid = f->dd_grid;

@@ -7,17 +7,25 @@
 // W = [G_0 .. G_m-1], V = [K_0 .. K_m-1]:
 //        Sigma[i][l] -= sum_q V[i][q] * W[l][q],   q < 2m, for every stored (i >= l) entry.
 //
-// HBM-bound streaming kernel (algorithmic traffic 16 B per stored entry; 4m fp64 flop per entry,
-// so the fp64 FMA pipe is a close second limiter at m = 20 - see DESIGN.md).  Structure:
+// Roofline: 16 B of HBM traffic and 4m fp64 flop per stored entry.  At m = 20 that is 3.2 GB and
+// 16.3 GFLOP per pass at N = 10,000: 0.49 ms at the measured 6.5 TB/s against 0.44 ms at the
+// fp64 peak (37 TFLOP/s), so BOTH limits bind and neither the FMA issue slots nor the shared-memory
+// operand traffic of a scalar DFMA loop can be afforded (round-1 profile, profiles/r3_*: the
+// DFMA version ran at 58 % fp64-pipe and 72 % shared-memory wavefront utilisation, 0.78 ms).
+// Structure of this version:
 //   * persistent CTAs (one per SM), each walks a contiguous range of 64-row x 128-column chunks
 //     of the column strips (ekf_layout.h); a chunk is one contiguous 64 KiB byte range;
-//   * a dedicated I/O warp moves chunks HBM -> shared memory -> HBM with 1-D bulk async copies
-//     (cp.async.bulk, the TMA engine; completion on mbarriers), two stages deep, so the eight
-//     compute warps never issue a global load or store;
-//   * the strip's W rows (128 x 2m) stay resident in shared memory for the whole strip walk;
-//     the chunk's V rows (64 x 2m) arrive with the chunk (L2-resident panels);
-//   * each compute thread owns an 8 x 4 register tile of the chunk and runs 2m rank-1 FMAs on
-//     it, operands read from shared memory as conflict-free 16-byte loads (4 x 8 lane grid).
+//   * the rank-2m product runs on the fp64 tensor path: mma.sync.m8n8k4.f64 (DMMA.8x8x4), 16
+//     accumulator tiles (32 x 32 of Sigma) per warp, 8 warps per chunk.  Per k-step a warp issues
+//     8 conflict-free LDS.64 fragment loads for 16 DMMAs (the DFMA loop needed 6 LDS.128 per
+//     32 DFMA per thread);
+//   * Sigma goes HBM -> registers -> HBM directly in accumulator-fragment order with 256-bit
+//     accesses (LDG.E.256 / STG.E.256): the row/column interleave of ekf_panel_slot() makes every
+//     thread own 4 contiguous doubles, every warp access 8 full 128-byte lines; the next chunk's
+//     tile is prefetched into a second register set while the current one is updated;
+//   * the strip's W rows (128 x 2m) stay resident in shared memory for the whole strip walk; the
+//     chunk's V rows (64 x 2m, L2-resident panels) arrive through a 3-stage bulk-copy
+//     (cp.async.bulk + mbarrier) ring driven by a dedicated producer warp.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -28,16 +36,14 @@ namespace ekf {
 
 constexpr int kDdComputeWarps = 8;
 constexpr int kDdComputeThreads = kDdComputeWarps * 32;
-constexpr int kDdThreads = kDdComputeThreads + 32;  // + one I/O warp
-constexpr int kDdStages = 2;
-constexpr int kChunkElems = EKF_CHUNK_ROWS * EKF_STRIP;           // 8192 doubles
-constexpr int kChunkBytes = kChunkElems * 8;                      // 64 KiB
+constexpr int kDdThreads = kDdComputeThreads + 32;  // + one producer warp
+constexpr int kDdVStages = 3;
 
 struct DdParams {
   double *sigma;
   const double *V;   // row operand  (K panels)
   const double *W;   // column operand (G panels)
-  int n_pad, kmax, k2;       // k2 = 2m panel columns in use
+  int n_pad, kmax, k2;       // k2 = panel columns in use, a multiple of 4
   int row_begin, row_end;    // rows handled by this launch (multiples of 64); whole matrix: 0, n_pad
   long long total_chunks;
 };
@@ -119,25 +125,37 @@ __device__ __forceinline__ void dd_advance(ChunkCursor &cur, int row_begin, int 
   if (cur.row >= row_end) { cur.J += 1; cur.row = strip_first_row(cur.J, row_begin); }
 }
 
-// Shared-memory carve-up (dynamic): [sigma stages][V-row stages][W strip rows][mbarriers]
+// Shared-memory carve-up (dynamic): [V-row stages][W strip rows][mbarriers]
 __host__ __device__ inline size_t dd_smem_bytes(int k2) {
-  return (size_t)kDdStages * kChunkBytes                       // sigma chunks
-         + (size_t)kDdStages * 2 * k2 * EKF_PBLK * 8           // V rows of the chunk: 2 blocks of 32 rows
+  return (size_t)kDdVStages * 2 * k2 * EKF_PBLK * 8           // V rows of the chunk: 2 blocks of 32 rows
          + (size_t)4 * k2 * EKF_PBLK * 8                       // W rows of the strip: 4 blocks of 32 rows
-         + 64;                                                 // mbarriers
+         + 128;                                                // mbarriers
 }
 
+__device__ __forceinline__ void ld256(const double *p, double &a, double &b, double &c, double &d) {
+  asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+__device__ __forceinline__ void st256(double *p, double a, double b, double c, double d) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+// D = A (8x4, row) * B (4x8, col) + C on the fp64 tensor path
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// k2 must be a multiple of 4 (the sequential kernel zero-fills the pad columns of an odd scan).
 __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int k2 = p.k2;
   const int blk_elems = k2 * EKF_PBLK;  // doubles per 32-row panel block in use
-  double *s_sig = reinterpret_cast<double *>(smem_raw);
-  double *s_v = s_sig + kDdStages * kChunkElems;
-  double *s_w = s_v + kDdStages * 2 * blk_elems;
+  double *s_v = reinterpret_cast<double *>(smem_raw);
+  double *s_w = s_v + kDdVStages * 2 * blk_elems;
   uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_w + 4 * blk_elems);
-  uint64_t *full = s_bar;          // [kDdStages] chunk + V rows landed
-  uint64_t *done = s_bar + 2;      // [kDdStages] compute warps finished the stage
-  uint64_t *wfull = s_bar + 4;     // strip W rows landed
+  uint64_t *full = s_bar;                  // [kDdVStages] V rows of the chunk landed
+  uint64_t *done = s_bar + kDdVStages;     // [kDdVStages] compute warps finished with the stage
+  uint64_t *wfull = s_bar + 2 * kDdVStages;  // strip W rows landed
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -146,7 +164,7 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
   const int n_chunks = (int)(c_end - c_begin);
 
   if (tid == 0) {
-    for (int s = 0; s < kDdStages; ++s) { mbar_init(&full[s], 1); mbar_init(&done[s], kDdComputeWarps); }
+    for (int s = 0; s < kDdVStages; ++s) { mbar_init(&full[s], 1); mbar_init(&done[s], kDdComputeWarps); }
     mbar_init(wfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -156,30 +174,18 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
   const uint32_t blk_bytes = (uint32_t)blk_elems * 8;
 
   if (warp == kDdComputeWarps) {
-    // ================= I/O warp: one elected lane drives the bulk-copy engine ==================
+    // ================= producer warp: one elected lane feeds the V-row ring ====================
     if ((tid & 31) == 0) {
-      ChunkCursor ld = dd_seek(c_begin, p.row_begin, p.row_end);   // next chunk to load
-      ChunkCursor st = ld;                                         // next chunk to store
-      for (int it = 0; it < n_chunks + kDdStages; ++it) {
-        const int s = it % kDdStages;
-        if (it >= kDdStages) {
-          // stage s holds the finished chunk it-kDdStages: write it back, then the buffer is free
-          mbar_wait(&done[s], ((it / kDdStages) - 1) & 1);
-          bulk_s2g(p.sigma + ekf_elem(p.n_pad, st.row, st.J * EKF_STRIP), s_sig + s * kChunkElems, kChunkBytes);
-          bulk_commit();
-          dd_advance(st, p.row_begin, p.row_end);
-          bulk_wait_read0();
-        }
-        if (it < n_chunks) {
-          mbar_expect_tx(&full[s], kChunkBytes + 2 * blk_bytes);
-          bulk_g2s(s_sig + s * kChunkElems, p.sigma + ekf_elem(p.n_pad, ld.row, ld.J * EKF_STRIP), kChunkBytes, &full[s]);
-          const int vb = ld.row / EKF_PBLK;
-          bulk_g2s(s_v + (s * 2 + 0) * blk_elems, p.V + (int64_t)vb * p.kmax * EKF_PBLK, blk_bytes, &full[s]);
-          bulk_g2s(s_v + (s * 2 + 1) * blk_elems, p.V + (int64_t)(vb + 1) * p.kmax * EKF_PBLK, blk_bytes, &full[s]);
-          dd_advance(ld, p.row_begin, p.row_end);
-        }
+      ChunkCursor ld = dd_seek(c_begin, p.row_begin, p.row_end);
+      for (int it = 0; it < n_chunks; ++it) {
+        const int s = it % kDdVStages;
+        if (it >= kDdVStages) mbar_wait(&done[s], ((it / kDdVStages) - 1) & 1);
+        mbar_expect_tx(&full[s], 2 * blk_bytes);
+        const int vb = ld.row / EKF_PBLK;
+        bulk_g2s(s_v + (s * 2 + 0) * blk_elems, p.V + (int64_t)vb * p.kmax * EKF_PBLK, blk_bytes, &full[s]);
+        bulk_g2s(s_v + (s * 2 + 1) * blk_elems, p.V + (int64_t)(vb + 1) * p.kmax * EKF_PBLK, blk_bytes, &full[s]);
+        dd_advance(ld, p.row_begin, p.row_end);
       }
-      bulk_wait_all0();
     }
     return;
   }
@@ -188,73 +194,81 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
   const int lane = tid & 31;
   const int wr = warp >> 2;        // 32-row block of the chunk (0..1)
   const int wc = warp & 3;         // 32-column block of the strip (0..3)
-  const int rg = lane >> 3;        // 0..3
-  const int g = lane & 7;          // 0..7
-  // thread rows: 32*wr + 8*pp + 2*rg + e  (pp 0..3, e 0..1); cols: 32*wc + 16*c + 2*g + f (c,f 0..1)
-  const double *vbase0 = s_v + wr * blk_elems + 2 * rg;
-  const double *wbase = s_w + wc * blk_elems + 2 * g;
+  const int g = lane >> 2;         // fragment row / column group (0..7)
+  const int t4 = lane & 3;         // fragment k index / column pair (0..3)
+  // accumulator tile (i, j), i, j = 0..3: row = 32 wr + row_of_slot(8 i + g), columns
+  // 32 wc + 16 (j >> 1) + 4 t4 + 2 (j & 1) + {0, 1}: the pair (j, j + 1) is 4 contiguous doubles.
+  int toff[4];                     // element offset of (tile row i, column pair 0) inside the chunk
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    toff[i] = (32 * wr + ekf_panel_row_of_slot(8 * i + g)) * EKF_STRIP + 32 * wc + 4 * t4;
 
   ChunkCursor cur = dd_seek(c_begin, p.row_begin, p.row_end);
+  double c[4][4][2], cn[4][4][2];
+  {
+    const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+        ld256(base + toff[i] + 16 * jj, c[i][2 * jj][0], c[i][2 * jj][1], c[i][2 * jj + 1][0], c[i][2 * jj + 1][1]);
+  }
   int loadedJ = -1;
   uint32_t wphase = 0;
+  const int ksteps = k2 >> 2;
   for (int it = 0; it < n_chunks; ++it) {
-    const int s = it % kDdStages;
-    if (cur.J != loadedJ) {
+    const int s = it % kDdVStages;
+    double *out = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+    const int curJ = cur.J;
+    dd_advance(cur, p.row_begin, p.row_end);
+    if (it + 1 < n_chunks) {       // prefetch the next chunk's tile into the second register set
+      const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+          ld256(base + toff[i] + 16 * jj, cn[i][2 * jj][0], cn[i][2 * jj][1], cn[i][2 * jj + 1][0], cn[i][2 * jj + 1][1]);
+    }
+    if (curJ != loadedJ) {
       // new strip: all compute warps must be done with the old W rows before they are replaced
       named_bar_sync(1, kDdComputeThreads);
       if (tid == 0) {
         mbar_expect_tx(wfull, 4 * blk_bytes);
         for (int b = 0; b < 4; ++b)
-          bulk_g2s(s_w + b * blk_elems, p.W + (int64_t)(cur.J * 4 + b) * p.kmax * EKF_PBLK, blk_bytes, wfull);
+          bulk_g2s(s_w + b * blk_elems, p.W + (int64_t)(curJ * 4 + b) * p.kmax * EKF_PBLK, blk_bytes, wfull);
       }
       mbar_wait(wfull, wphase);
       wphase ^= 1;
-      loadedJ = cur.J;
+      loadedJ = curJ;
     }
-    mbar_wait(&full[s], (it / kDdStages) & 1);
+    mbar_wait(&full[s], (it / kDdVStages) & 1);
 
-    double *tile = s_sig + s * kChunkElems + (32 * wr + 2 * rg) * EKF_STRIP + 32 * wc + 2 * g;
-    double2 acc[4][2][2];  // [pp][e][c] -> (f = x, y)
-#pragma unroll
-    for (int pp = 0; pp < 4; ++pp)
-#pragma unroll
-      for (int e = 0; e < 2; ++e)
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-          acc[pp][e][c] = *reinterpret_cast<const double2 *>(tile + (8 * pp + e) * EKF_STRIP + 16 * c);
-
-    const double *vb = vbase0 + s * 2 * blk_elems;
+    const double *va = s_v + (s * 2 + wr) * blk_elems + lane;
+    const double *wb = s_w + wc * blk_elems + lane;
 #pragma unroll 2
-    for (int q = 0; q < k2; ++q) {
-      double2 v[4], w[2];
+    for (int ks = 0; ks < ksteps; ++ks) {
+      double a[4], b[4];
 #pragma unroll
-      for (int pp = 0; pp < 4; ++pp) v[pp] = *reinterpret_cast<const double2 *>(vb + q * EKF_PBLK + 8 * pp);
+      for (int i = 0; i < 4; ++i) a[i] = -va[ks * 128 + i * 32];
 #pragma unroll
-      for (int c = 0; c < 2; ++c) w[c] = *reinterpret_cast<const double2 *>(wbase + q * EKF_PBLK + 16 * c);
+      for (int j = 0; j < 4; ++j) b[j] = wb[ks * 128 + j * 32];
 #pragma unroll
-      for (int pp = 0; pp < 4; ++pp)
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          acc[pp][0][c].x = fma(-v[pp].x, w[c].x, acc[pp][0][c].x);
-          acc[pp][0][c].y = fma(-v[pp].x, w[c].y, acc[pp][0][c].y);
-          acc[pp][1][c].x = fma(-v[pp].y, w[c].x, acc[pp][1][c].x);
-          acc[pp][1][c].y = fma(-v[pp].y, w[c].y, acc[pp][1][c].y);
-        }
+        for (int j = 0; j < 4; ++j) dmma884(c[i][j][0], c[i][j][1], a[i], b[j]);
     }
-
-#pragma unroll
-    for (int pp = 0; pp < 4; ++pp)
-#pragma unroll
-      for (int e = 0; e < 2; ++e)
-#pragma unroll
-        for (int c = 0; c < 2; ++c)
-          *reinterpret_cast<double2 *>(tile + (8 * pp + e) * EKF_STRIP + 16 * c) = acc[pp][e][c];
-
-    // make the generic-proxy writes visible to the bulk-copy engine, then hand the stage over
-    fence_proxy_async();
     __syncwarp();
     if (lane == 0) mbar_arrive(&done[s]);
-    dd_advance(cur, p.row_begin, p.row_end);
+
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj)
+        st256(out + toff[i] + 16 * jj, c[i][2 * jj][0], c[i][2 * jj][1], c[i][2 * jj + 1][0], c[i][2 * jj + 1][1]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { c[i][j][0] = cn[i][j][0]; c[i][j][1] = cn[i][j][1]; }
   }
 }
 

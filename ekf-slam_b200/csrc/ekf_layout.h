@@ -50,9 +50,21 @@ EKF_HD int64_t ekf_elem(int n_pad, int i, int j) {
 EKF_HD int64_t ekf_elem_sym(int n_pad, int i, int j) {
   return i >= j ? ekf_elem(n_pad, i, j) : ekf_elem(n_pad, j, i);
 }
-/* W / V panels: n_pad rows x kmax columns, blocked [row/32][k][row%32] */
+/* W / V panels: n_pad rows x kmax columns (kmax a multiple of 4), laid out for the fp64 tensor-core
+ * fragments of the covariance pass (mma.m8n8k4): [row / 32][k / 4][slot(row % 32)][k % 4].
+ *   - a 32-row block of the first k2 columns is one contiguous range of k2 * 256 bytes (one bulk copy);
+ *   - inside a k-step (4 columns) a row's 4 values are contiguous (32 B), and the 8 rows of one
+ *     8 x 4 fragment are 8 consecutive slots: a fragment load is one conflict-free 256-byte
+ *     warp-wide LDS.64 (lane l reads double l of the 8-slot group);
+ *   - slot() interleaves the rows so that the four columns {4t .. 4t+3} a thread owns in two adjacent
+ *     8-column tiles are contiguous in Sigma (one 256-bit load / store per thread):
+ *         row = 16*jj + 4*t + 2*jb + e   ->   slot = 16*jj + 8*jb + 2*t + e.
+ *     Rows (a, a+1) of one landmark (a even) stay in adjacent slots. */
+EKF_HD int ekf_panel_slot(int r) { return (r & 16) | ((r & 2) << 2) | ((r >> 1) & 6) | (r & 1); }
+/* inverse: row (0..31) held by a slot */
+EKF_HD int ekf_panel_row_of_slot(int s) { return (s & 16) | ((s & 6) << 1) | ((s >> 2) & 2) | (s & 1); }
 EKF_HD int64_t ekf_panel_elem(int kmax, int row, int k) {
-  return ((int64_t)(row / EKF_PBLK) * kmax + k) * EKF_PBLK + (row % EKF_PBLK);
+  return (((int64_t)(row >> 5) * (kmax >> 2) + (k >> 2)) << 7) + (ekf_panel_slot(row & 31) << 2) + (k & 3);
 }
 
 #endif

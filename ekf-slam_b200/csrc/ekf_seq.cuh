@@ -22,9 +22,16 @@
 //
 // Parallel decomposition: a cooperative grid; thread g owns landmarks g, g+T, ... (their two
 // state entries, pose-panel rows, diagonal block, panel rows).  The 3 pose rows are tracked
-// redundantly by every CTA in shared memory.  Exactly ONE grid barrier per measurement: local
-// arg-min -> slot -> barrier -> every CTA reduces the slots identically, reads the chosen
-// landmark's data through L2 (ld.cg) and proceeds on its own rows.
+// redundantly by every CTA in shared memory.  Exactly ONE grid barrier per measurement.  The
+// phase is latency-bound (one dependent chain per measurement), so the chain is kept short:
+//   * association already forms, for every candidate, the linearisation, S and S^-1 the update
+//     needs; each CTA publishes its best candidate TOGETHER with that record (22 doubles) in its
+//     slot before the barrier, so after the barrier nothing is recomputed serially: every warp
+//     reduces the slots (one L2 round trip), then warp 0 fetches the winner's record while warp 1
+//     fetches the winner's panel-row history (a second, shared L2 round trip);
+//   * the gather of the two landmark columns from Sigma_0 (HBM latency) and the panel-history
+//     loads of the correction are issued together, 256 bits at a time;
+//   * a new landmark / known association takes the (rare) serial path through thread 0.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -71,7 +78,14 @@ struct SeqParams {
   unsigned long long bar_base;
   double *slot_d;  // 2 * gridDim
   int *slot_k;     // 2 * gridDim
+  double *slot_rec;  // 2 * gridDim * kRecStride: the slot candidate's update record
 };
+
+// update record of one (measurement, landmark) pair: everything the row update needs
+//   [0..3] h0[1..4]  [4..7] h1[1..4]  [8..13] T[0..2][0..1] (pose rows of G)  [14..16] S^-1
+//   [17..18] innovation  [19..21] the landmark's current diagonal block (aa, ba, bb)
+constexpr int kRecDoubles = 22;
+constexpr int kRecStride = 24;
 
 __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long target) {
   __syncthreads();
@@ -95,31 +109,36 @@ __device__ __forceinline__ double4 ldcg_d4(const double4 *p) {
   return v;
 }
 
-// Everything a CTA's threads need to process their rows for the current measurement.
+// Shared per-measurement broadcast: the chosen landmark and its update record.
 struct Bcast {
   int j;        // associated landmark, or -1 when the measurement is skipped
   int is_new;   // the landmark's state is (re)initialised from the sighting
-  Lin L;        // linearisation at landmark j
-  double lx, ly;        // landmark j position used (after initialisation)
-  double m00, m01, m11; // S^-1
-  double zd0, zd1;      // innovation, bearing wrapped
-  double Tp[3][2];      // pose rows of G
-  double daa, dba, dbb; // diagonal block of landmark j (current)
+  double lx, ly;             // landmark j position used when is_new
+  double rec[kRecStride];    // update record (layout above)
 };
+
+__device__ __forceinline__ double ld_plain256(const double *p, double &a, double &b, double &c) {
+  double d;
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p) : "memory");
+  return d;
+}
 
 __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p) {
   __shared__ double s_ps[3];      // pose state (theta, x, y)
   __shared__ double s_pb[3][3];   // pose block of Sigma_cur, full symmetric
   __shared__ Cand s_red[kSeqThreads / 32];
+  __shared__ double s_wrec[kSeqThreads / 32][kRecStride];   // each warp's best candidate record
   __shared__ Bcast s_b;
   __shared__ double s_wa[kMaxK2], s_wb[kMaxK2];
   __shared__ int s_cnt;
   __shared__ double s_pred[2];    // (-dy, dx)
 
   const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
   const int nthreads_total = gridDim.x * blockDim.x;
   const int gtid = blockIdx.x * blockDim.x + tid;
   const int n_pad = p.n_pad;
+  const int nks = p.kmax >> 2;     // k-steps per panel block
   double *const strip0 = p.sigma;  // strip 0 starts at offset 0: row i at i*128
 
   // ---------------- phase 0: pose injection, prediction, extraction of Pp / D -------------
@@ -193,17 +212,22 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   }
 
   // ---------------- measurement loop --------------------------------------------------------
+  const bool unknown = (p.ids == nullptr);
+  const int G = (int)gridDim.x;
   for (int t = 0; t < p.m; ++t) {
     const double mx = p.xy[2 * t], my = p.xy[2 * t + 1];
     const Polar z = to_polar(mx, my);                        // slam.cpp:345-347
     const double th = s_ps[0], px = s_ps[1], py = s_ps[2];
     const int cnt = s_cnt;
-    const bool unknown = (p.ids == nullptr);
     const int par = t & 1;
 
-    // ---- A: Mahalanobis distance to every mapped landmark (own ones), local arg-min ------
+    // ---- A: Mahalanobis distance to every mapped landmark (own ones); the best candidate keeps
+    //         its update record in registers --------------------------------------------------------
     if (unknown) {
       Cand best{INFINITY, 0x7fffffff};
+      double rec[kRecDoubles];
+#pragma unroll
+      for (int i = 0; i < kRecDoubles; ++i) rec[i] = 0.0;
       for (int k = gtid; k < cnt; k += nthreads_total) {
         const int a = 4 + 2 * k;
         const double2 lm = *reinterpret_cast<const double2 *>(p.mu + a);
@@ -215,50 +239,117 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
         const Innov I = innovation(B, L, p.r_noise);         // slam.cpp:395
         const double zd0 = z.r - L.zhat_r;
         const double zd1 = normalize_angle(z.phi - L.zhat_b);  // slam.cpp:398-399
-        const double d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1);  // slam.cpp:401
-        best = cand_min(best, Cand{d, k});
-      }
-      best = warp_argmin(best);
-      if ((tid & 31) == 0) s_red[tid >> 5] = best;
-      __syncthreads();
-      if (tid == 0) {
-        Cand c = s_red[0];
+        double i00, i01, i11;
+        const double d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);  // slam.cpp:401
+        const Cand c{d, k};
+        const Cand nb = cand_min(best, c);
+        if (nb.k == k) {                                     // this candidate is the thread's best so far
 #pragma unroll
-        for (int w = 1; w < kSeqThreads / 32; ++w) c = cand_min(c, s_red[w]);
-        p.slot_d[par * gridDim.x + blockIdx.x] = c.d;
-        p.slot_k[par * gridDim.x + blockIdx.x] = c.k;
+          for (int q = 0; q < 4; ++q) { rec[q] = L.h0[q + 1]; rec[4 + q] = L.h1[q + 1]; }
+#pragma unroll
+          for (int q = 0; q < 3; ++q) { rec[8 + 2 * q] = I.T[q][0]; rec[9 + 2 * q] = I.T[q][1]; }
+          rec[14] = i00; rec[15] = i01; rec[16] = i11;
+          rec[17] = zd0; rec[18] = zd1;
+          rec[19] = dk.x; rec[20] = dk.y; rec[21] = dk.z;
+        }
+        best = nb;
+      }
+      const Cand wbest = warp_argmin(best);
+      if (best.k == wbest.k && best.k != 0x7fffffff) {
+#pragma unroll
+        for (int i = 0; i < kRecDoubles; ++i) s_wrec[warp][i] = rec[i];
+      }
+      if (lane == 0) s_red[warp] = wbest;
+      __syncthreads();
+      if (warp == 0) {
+        Cand c = s_red[0];
+        int bw = 0;
+#pragma unroll
+        for (int w = 1; w < kSeqThreads / 32; ++w) {
+          const Cand o = s_red[w];
+          const Cand n2 = cand_min(c, o);
+          if (n2.k != c.k) bw = w;
+          c = n2;
+        }
+        double *dst = p.slot_rec + (int64_t)(par * G + blockIdx.x) * kRecStride;
+        if (lane < kRecDoubles) dst[lane] = s_wrec[bw][lane];
+        if (lane == 0) {
+          p.slot_d[par * G + blockIdx.x] = c.d;
+          p.slot_k[par * G + blockIdx.x] = c.k;
+        }
       }
     }
 
     // ---- B: the one grid barrier of this measurement ----------------------------------------
     grid_barrier(p.bar, p.bar_base + (unsigned long long)(t + 1) * gridDim.x);
 
-    // ---- C: decision + linearisation at the chosen landmark (identical in every CTA) --------
-    if (tid < 32) {
-      int j = -1, is_new = 0, err = 0;
-      if (unknown) {
-        Cand c{INFINITY, 0x7fffffff};
-        for (int b = tid; b < (int)gridDim.x; b += 32)
-          c = cand_min(c, Cand{ldcg_d(p.slot_d + par * gridDim.x + b), __ldcg(p.slot_k + par * gridDim.x + b)});
-        c = warp_argmin(c);
-        // the tentative landmark sits last with distance == threshold and wins only on a
-        // strictly smaller value: slam.cpp:406-408,418-440
-        if (c.d <= p.thr && c.k < cnt) j = c.k;
-        else if (cnt < p.N) { j = cnt; is_new = 1; }
-        else err = kErrCapacity;
-      } else {
-        const int id = p.ids[t];
-        const bool del = p.action != nullptr && p.action[t] == 2;   // slam.cpp:205
-        if (!del) {
-          if (id < 0 || id >= p.N) err = kErrBadId;
-          else {
-            j = id;
-            // first sighting: both state slots exactly zero (slam.cpp:213)
-            is_new = (ldcg_d(p.mu + 4 + 2 * id) == 0.0 && ldcg_d(p.mu + 5 + 2 * id) == 0.0);
+    // ---- C: decision (identical in every warp of every CTA) + the winner's record ------------
+    bool fast = false;   // matched an existing landmark: record comes from the winner's slot
+    int jfast = -1;
+    if (unknown) {
+      Cand c{INFINITY, 0x7fffffff};
+      int bstar = 0;
+      for (int b = lane; b < G; b += 32) {
+        const Cand o{ldcg_d(p.slot_d + par * G + b), __ldcg(p.slot_k + par * G + b)};
+        const Cand n2 = cand_min(c, o);
+        if (n2.k != c.k) bstar = b;
+        c = n2;
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        Cand o;
+        o.d = __shfl_xor_sync(0xffffffffu, c.d, off);
+        o.k = __shfl_xor_sync(0xffffffffu, c.k, off);
+        const int ob = __shfl_xor_sync(0xffffffffu, bstar, off);
+        const Cand n2 = cand_min(c, o);
+        if (n2.k != c.k) bstar = ob;
+        c = n2;
+      }
+      // the tentative landmark sits last with distance == threshold and wins only on a
+      // strictly smaller value: slam.cpp:406-408,418-440
+      fast = (c.d <= p.thr && c.k < cnt);
+      if (fast) {
+        jfast = c.k;
+        if (warp == 0) {
+          if (lane < kRecDoubles)
+            s_b.rec[lane] = ldcg_d(p.slot_rec + (int64_t)(par * G + bstar) * kRecStride + lane);
+          if (lane == 0) {
+            s_b.j = jfast; s_b.is_new = 0;
+            if (blockIdx.x == 0 && p.assoc_out) p.assoc_out[t] = jfast;
+          }
+        } else if (warp == 1 || kSeqThreads == 32) {
+          // panel history of the chosen landmark's two rows (column operand of the correction)
+          const int a = 4 + 2 * jfast;
+          const double *wrow = p.W + (((int64_t)(a >> 5) * nks) << 7) + (ekf_panel_slot(a & 31) << 2);
+          for (int i = lane; i < 8 * ((t + 1) >> 1); i += 32) {   // 8 doubles per k-step, q < 2t
+            const int ks = i >> 3, w = i & 7, q = 4 * ks + (w & 3);
+            if (q < 2 * t) {
+              const double v = ldcg_d(wrow + ((int64_t)ks << 7) + w);
+              if (w < 4) s_wa[q] = v; else s_wb[q] = v;
+            }
           }
         }
       }
+    }
+    if (!fast) {
+      // serial path (thread 0): new landmark, known association, skipped sighting, errors
       if (tid == 0) {
+        int j = -1, is_new = 0, err = 0;
+        if (unknown) {
+          if (cnt < p.N) { j = cnt; is_new = 1; }
+          else err = kErrCapacity;
+        } else {
+          const int id = p.ids[t];
+          const bool del = p.action != nullptr && p.action[t] == 2;   // slam.cpp:205
+          if (!del) {
+            if (id < 0 || id >= p.N) err = kErrBadId;
+            else {
+              j = id;
+              // first sighting: both state slots exactly zero (slam.cpp:213)
+              is_new = (ldcg_d(p.mu + 4 + 2 * id) == 0.0 && ldcg_d(p.mu + 5 + 2 * id) == 0.0);
+            }
+          }
+        }
         s_b.j = j; s_b.is_new = is_new;
         if (err && blockIdx.x == 0) atomicMax(p.status, err);
         if (blockIdx.x == 0 && p.assoc_out) p.assoc_out[t] = j;
@@ -277,87 +368,94 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
           const double par3[3] = {pa.x, pa.y, pa.z}, pbr3[3] = {pbr.x, pbr.y, pbr.z};
           const Block5 B = make_block5(s_pb, par3, pbr3, dj.x, dj.y, dj.z);
           const Innov I = innovation(B, L, p.r_noise);       // S = H Sigma H^T + R, slam.cpp:476
-          const double det = I.s00 * I.s11 - I.s01 * I.s01;
-          const double m00 = I.s11 / det, m01 = -I.s01 / det, m11 = I.s00 / det;
           const double zd0 = z.r - L.zhat_r;
           const double zd1 = normalize_angle(z.phi - L.zhat_b);   // slam.cpp:479-480
-          s_b.L = L; s_b.lx = lx; s_b.ly = ly;
-          s_b.m00 = m00; s_b.m01 = m01; s_b.m11 = m11;
-          s_b.zd0 = zd0; s_b.zd1 = zd1;
-          s_b.daa = dj.x; s_b.dba = dj.y; s_b.dbb = dj.z;
-          // pose rows: gain, state and pose-block update (slam.cpp:476,482,485-486 restricted
-          // to rows/cols 0..2), done redundantly by every CTA
-          double Kp[3][2];
+          double i00, i01, i11;
+          (void)mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
+          s_b.lx = lx; s_b.ly = ly;
 #pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            s_b.Tp[c][0] = I.T[c][0]; s_b.Tp[c][1] = I.T[c][1];
-            Kp[c][0] = I.T[c][0] * m00 + I.T[c][1] * m01;
-            Kp[c][1] = I.T[c][0] * m01 + I.T[c][1] * m11;
-          }
-          double ps_new[3];
+          for (int q = 0; q < 4; ++q) { s_b.rec[q] = L.h0[q + 1]; s_b.rec[4 + q] = L.h1[q + 1]; }
 #pragma unroll
-          for (int c = 0; c < 3; ++c) ps_new[c] = s_ps[c] + (Kp[c][0] * zd0 + Kp[c][1] * zd1);
-          ps_new[0] = normalize_angle(ps_new[0]);            // slam.cpp:488
-#pragma unroll
-          for (int c = 0; c < 3; ++c)
-#pragma unroll
-            for (int c2 = 0; c2 <= c; ++c2) {
-              const double v = s_pb[c][c2] - (Kp[c][0] * I.T[c2][0] + Kp[c][1] * I.T[c2][1]);
-              s_pb[c][c2] = v; s_pb[c2][c] = v;
-            }
-#pragma unroll
-          for (int c = 0; c < 3; ++c) s_ps[c] = ps_new[c];
-          if (blockIdx.x == 0) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              p.W[ekf_panel_elem(p.kmax, c, 2 * t)] = I.T[c][0];
-              p.W[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = I.T[c][1];
-              p.V[ekf_panel_elem(p.kmax, c, 2 * t)] = Kp[c][0];
-              p.V[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = Kp[c][1];
-              p.Pp[c] = make_double4(s_pb[c][0], s_pb[c][1], s_pb[c][2], 0.0);
-            }
-          }
-        } else if (blockIdx.x == 0) {
-#pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            p.W[ekf_panel_elem(p.kmax, c, 2 * t)] = 0.0; p.W[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = 0.0;
-            p.V[ekf_panel_elem(p.kmax, c, 2 * t)] = 0.0; p.V[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = 0.0;
+          for (int q = 0; q < 3; ++q) { s_b.rec[8 + 2 * q] = I.T[q][0]; s_b.rec[9 + 2 * q] = I.T[q][1]; }
+          s_b.rec[14] = i00; s_b.rec[15] = i01; s_b.rec[16] = i11;
+          s_b.rec[17] = zd0; s_b.rec[18] = zd1;
+          s_b.rec[19] = dj.x; s_b.rec[20] = dj.y; s_b.rec[21] = dj.z;
+        }
+      }
+      __syncthreads();
+      const int js = s_b.j;
+      if (js >= 0) {
+        const int a = 4 + 2 * js;
+        const double *wrow = p.W + (((int64_t)(a >> 5) * nks) << 7) + (ekf_panel_slot(a & 31) << 2);
+        for (int i = tid; i < 8 * ((t + 1) >> 1); i += blockDim.x) {
+          const int ks = i >> 3, w = i & 7, q = 4 * ks + (w & 3);
+          if (q < 2 * t) {
+            const double v = ldcg_d(wrow + ((int64_t)ks << 7) + w);
+            if (w < 4) s_wa[q] = v; else s_wb[q] = v;
           }
         }
       }
     }
     __syncthreads();
     const int j = s_b.j;
-    // panel history of the chosen landmark's two rows (column operand of the correction)
-    if (j >= 0) {
-      const int a = 4 + 2 * j;
-      for (int q = tid; q < 2 * t; q += blockDim.x) {
-        s_wa[q] = ldcg_d(p.W + ekf_panel_elem(p.kmax, a, q));
-        s_wb[q] = ldcg_d(p.W + ekf_panel_elem(p.kmax, a + 1, q));
+
+    // ---- pose rows: gain, state and pose-block update (slam.cpp:476,482,485-486 restricted to
+    //      rows/cols 0..2), redundantly in every CTA, one lane per pose row ------------------------
+    if (warp == 0 && lane < 3) {
+      const int c = lane;
+      if (j >= 0) {
+        const double m00 = s_b.rec[14], m01 = s_b.rec[15], m11 = s_b.rec[16];
+        const double zd0 = s_b.rec[17], zd1 = s_b.rec[18];
+        const double t0 = s_b.rec[8 + 2 * c], t1 = s_b.rec[9 + 2 * c];
+        const double k0 = t0 * m00 + t1 * m01, k1 = t0 * m01 + t1 * m11;
+        double psn = s_ps[c] + (k0 * zd0 + k1 * zd1);
+        if (c == 0) psn = normalize_angle(psn);              // slam.cpp:488
+        for (int c2 = 0; c2 <= c; ++c2) {
+          const double v = s_pb[c][c2] - (k0 * s_b.rec[8 + 2 * c2] + k1 * s_b.rec[9 + 2 * c2]);
+          s_pb[c][c2] = v; s_pb[c2][c] = v;
+        }
+        s_ps[c] = psn;
+        if (blockIdx.x == 0) {
+          p.W[ekf_panel_elem(p.kmax, c, 2 * t)] = t0;
+          p.W[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = t1;
+          p.V[ekf_panel_elem(p.kmax, c, 2 * t)] = k0;
+          p.V[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = k1;
+        }
+      } else if (blockIdx.x == 0) {
+        p.W[ekf_panel_elem(p.kmax, c, 2 * t)] = 0.0; p.W[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = 0.0;
+        p.V[ekf_panel_elem(p.kmax, c, 2 * t)] = 0.0; p.V[ekf_panel_elem(p.kmax, c, 2 * t + 1)] = 0.0;
       }
     }
-    __syncthreads();
 
     // ---- D: own rows: gather the two landmark columns, gain, state, Pp, D, panels ------------
     if (j < 0) {
       for (int k = gtid; k < p.N; k += nthreads_total) {
         const int a = 4 + 2 * k;
         const double2 zero = make_double2(0.0, 0.0);
-        *reinterpret_cast<double2 *>(p.W + ekf_panel_elem(p.kmax, a, 2 * t)) = zero;
-        *reinterpret_cast<double2 *>(p.W + ekf_panel_elem(p.kmax, a, 2 * t + 1)) = zero;
-        *reinterpret_cast<double2 *>(p.V + ekf_panel_elem(p.kmax, a, 2 * t)) = zero;
-        *reinterpret_cast<double2 *>(p.V + ekf_panel_elem(p.kmax, a, 2 * t + 1)) = zero;
+        double *wp = p.W + ekf_panel_elem(p.kmax, a, 2 * t);
+        double *vp = p.V + ekf_panel_elem(p.kmax, a, 2 * t);
+        *reinterpret_cast<double2 *>(wp) = zero; *reinterpret_cast<double2 *>(wp + 4) = zero;
+        *reinterpret_cast<double2 *>(vp) = zero; *reinterpret_cast<double2 *>(vp + 4) = zero;
       }
     } else {
-      const Lin L = s_b.L;
-      const double m00 = s_b.m00, m01 = s_b.m01, m11 = s_b.m11;
-      const double zd0 = s_b.zd0, zd1 = s_b.zd1;
+      Lin L;
+      L.h0[0] = 0.0; L.h1[0] = -1.0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { L.h0[q + 1] = s_b.rec[q]; L.h1[q + 1] = s_b.rec[4 + q]; }
+      const double tp00 = s_b.rec[8], tp01 = s_b.rec[9], tp10 = s_b.rec[10], tp11 = s_b.rec[11];
+      const double tp20 = s_b.rec[12], tp21 = s_b.rec[13];
+      const double m00 = s_b.rec[14], m01 = s_b.rec[15], m11 = s_b.rec[16];
+      const double zd0 = s_b.rec[17], zd1 = s_b.rec[18];
       const int aj = 4 + 2 * j;
+      const int full_ks = (2 * t) >> 2;          // complete k-steps of panel history
+      const bool tail = ((2 * t) & 2) != 0;      // + two more columns
       for (int k = gtid; k < p.N; k += nthreads_total) {
         const int a = 4 + 2 * k;
         double q00, q01, q10, q11;  // Sigma_cur[{a,b}_k, {a,b}_j]
+        double *vrow = p.V + (((int64_t)(a >> 5) * nks) << 7) + (ekf_panel_slot(a & 31) << 2);
+        double *wrow = p.W + (((int64_t)(a >> 5) * nks) << 7) + (ekf_panel_slot(a & 31) << 2);
         if (k == j) {
-          q00 = s_b.daa; q01 = s_b.dba; q10 = s_b.dba; q11 = s_b.dbb;
+          q00 = s_b.rec[19]; q01 = s_b.rec[20]; q10 = s_b.rec[20]; q11 = s_b.rec[21];
         } else {
           if (k > j) {
             const double *src = p.sigma + ekf_elem(n_pad, a, aj);
@@ -370,13 +468,24 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
             const double2 c1 = __ldg(reinterpret_cast<const double2 *>(src + EKF_STRIP));
             q00 = c0.x; q10 = c0.y; q01 = c1.x; q11 = c1.y;
           }
-          // deferred downdates of earlier measurements of this scan
-          const double *vrow = p.V + ekf_panel_elem(p.kmax, a, 0);
-          for (int q = 0; q < 2 * t; ++q) {
-            const double2 v = *reinterpret_cast<const double2 *>(vrow + (int64_t)q * EKF_PBLK);
-            const double wa = s_wa[q], wb = s_wb[q];
-            q00 -= v.x * wa; q01 -= v.x * wb;
-            q10 -= v.y * wa; q11 -= v.y * wb;
+          // deferred downdates of earlier measurements of this scan: rows a, a+1 of V are 8
+          // contiguous doubles per k-step (this thread wrote them itself)
+          for (int ks = 0; ks < full_ks; ++ks) {
+            double va0, va1, va2, va3, vb0, vb1, vb2, vb3;
+            va3 = ld_plain256(vrow + ((int64_t)ks << 7), va0, va1, va2);
+            vb3 = ld_plain256(vrow + ((int64_t)ks << 7) + 4, vb0, vb1, vb2);
+            const double *wa = s_wa + 4 * ks, *wb = s_wb + 4 * ks;
+            q00 -= va0 * wa[0]; q01 -= va0 * wb[0]; q10 -= vb0 * wa[0]; q11 -= vb0 * wb[0];
+            q00 -= va1 * wa[1]; q01 -= va1 * wb[1]; q10 -= vb1 * wa[1]; q11 -= vb1 * wb[1];
+            q00 -= va2 * wa[2]; q01 -= va2 * wb[2]; q10 -= vb2 * wa[2]; q11 -= vb2 * wb[2];
+            q00 -= va3 * wa[3]; q01 -= va3 * wb[3]; q10 -= vb3 * wa[3]; q11 -= vb3 * wb[3];
+          }
+          if (tail) {
+            const double2 va = *reinterpret_cast<const double2 *>(vrow + ((int64_t)full_ks << 7));
+            const double2 vb = *reinterpret_cast<const double2 *>(vrow + ((int64_t)full_ks << 7) + 4);
+            const double *wa = s_wa + 4 * full_ks, *wb = s_wb + 4 * full_ks;
+            q00 -= va.x * wa[0]; q01 -= va.x * wb[0]; q10 -= vb.x * wa[0]; q11 -= vb.x * wb[0];
+            q00 -= va.y * wa[1]; q01 -= va.y * wb[1]; q10 -= vb.y * wa[1]; q11 -= vb.y * wb[1];
           }
         }
         double4 pa = p.Pp[a], pbr = p.Pp[a + 1];
@@ -393,25 +502,46 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
         lm.y = lm.y + (kb0 * zd0 + kb1 * zd1);
         *reinterpret_cast<double2 *>(p.mu + a) = lm;
         // Sigma_cur[i, pose c] -= K[i,:] . G[c,:]
-        pa.x -= ka0 * s_b.Tp[0][0] + ka1 * s_b.Tp[0][1];
-        pa.y -= ka0 * s_b.Tp[1][0] + ka1 * s_b.Tp[1][1];
-        pa.z -= ka0 * s_b.Tp[2][0] + ka1 * s_b.Tp[2][1];
-        pbr.x -= kb0 * s_b.Tp[0][0] + kb1 * s_b.Tp[0][1];
-        pbr.y -= kb0 * s_b.Tp[1][0] + kb1 * s_b.Tp[1][1];
-        pbr.z -= kb0 * s_b.Tp[2][0] + kb1 * s_b.Tp[2][1];
+        pa.x -= ka0 * tp00 + ka1 * tp01;
+        pa.y -= ka0 * tp10 + ka1 * tp11;
+        pa.z -= ka0 * tp20 + ka1 * tp21;
+        pbr.x -= kb0 * tp00 + kb1 * tp01;
+        pbr.y -= kb0 * tp10 + kb1 * tp11;
+        pbr.z -= kb0 * tp20 + kb1 * tp21;
         p.Pp[a] = pa; p.Pp[a + 1] = pbr;
         double4 dk = p.D[k];
         dk.x -= ka0 * ga0 + ka1 * ga1;
         dk.y -= kb0 * ga0 + kb1 * ga1;
         dk.z -= kb0 * gb0 + kb1 * gb1;
         p.D[k] = dk;
-        *reinterpret_cast<double2 *>(p.W + ekf_panel_elem(p.kmax, a, 2 * t)) = make_double2(ga0, gb0);
-        *reinterpret_cast<double2 *>(p.W + ekf_panel_elem(p.kmax, a, 2 * t + 1)) = make_double2(ga1, gb1);
-        *reinterpret_cast<double2 *>(p.V + ekf_panel_elem(p.kmax, a, 2 * t)) = make_double2(ka0, kb0);
-        *reinterpret_cast<double2 *>(p.V + ekf_panel_elem(p.kmax, a, 2 * t + 1)) = make_double2(ka1, kb1);
+        // columns 2t, 2t+1 of rows a (slot s) and a+1 (slot s+1) of both panels
+        double *wp = wrow + ((int64_t)((2 * t) >> 2) << 7) + ((2 * t) & 3);
+        double *vp = vrow + ((int64_t)((2 * t) >> 2) << 7) + ((2 * t) & 3);
+        *reinterpret_cast<double2 *>(wp) = make_double2(ga0, ga1);
+        *reinterpret_cast<double2 *>(wp + 4) = make_double2(gb0, gb1);
+        *reinterpret_cast<double2 *>(vp) = make_double2(ka0, ka1);
+        *reinterpret_cast<double2 *>(vp + 4) = make_double2(kb0, kb1);
       }
     }
-    __syncthreads();  // s_b / s_wa are rewritten by the next measurement
+    __syncthreads();  // s_b / s_wa / s_ps are rewritten by the next measurement
+  }
+
+  // pad columns [2m, round-up-to-4(2m)) of both panels are zeroed: the covariance pass works on
+  // whole k-steps of 4 columns
+  if ((2 * p.m) & 2) {
+    const int qz = 2 * p.m;
+    const double2 zero = make_double2(0.0, 0.0);
+    for (int k = gtid; k < p.N; k += nthreads_total) {
+      const int a = 4 + 2 * k;
+      double *wp = p.W + ekf_panel_elem(p.kmax, a, qz);
+      double *vp = p.V + ekf_panel_elem(p.kmax, a, qz);
+      *reinterpret_cast<double2 *>(wp) = zero; *reinterpret_cast<double2 *>(wp + 4) = zero;
+      *reinterpret_cast<double2 *>(vp) = zero; *reinterpret_cast<double2 *>(vp + 4) = zero;
+    }
+    if (blockIdx.x == 0 && tid < 3) {
+      p.W[ekf_panel_elem(p.kmax, tid, qz)] = 0.0; p.W[ekf_panel_elem(p.kmax, tid, qz + 1)] = 0.0;
+      p.V[ekf_panel_elem(p.kmax, tid, qz)] = 0.0; p.V[ekf_panel_elem(p.kmax, tid, qz + 1)] = 0.0;
+    }
   }
 
   // ---------------- epilogue: slam.cpp:273-274,291 / :490-491,508 ---------------------------------
