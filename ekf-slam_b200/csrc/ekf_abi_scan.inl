@@ -32,10 +32,18 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
     dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
     dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;  // whole k-steps; pad columns are zero
     dp.row_begin = 0; dp.row_end = f->n_pad;
-    dp.total_chunks = dd_total_chunks(f->n_pad, 0, f->n_pad);
-    long long grid = f->dd_grid;
-    if (grid > dp.total_chunks) grid = dp.total_chunks;
-    ekf_downdate_kernel<<<(unsigned)grid, kDdThreads, dd_smem_bytes(dp.k2), f->stream>>>(dp);
+    dp.prefetch_ahead = f->dd_prefetch;
+    if (f->dd_variant == 0) {
+      dp.total_chunks = dd_total_chunks(64, 0, f->n_pad);
+      long long grid = f->dd_grid;
+      if (grid > dp.total_chunks) grid = dp.total_chunks;
+      ekf_downdate_kernel<64, true><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
+    } else {
+      dp.total_chunks = dd_total_chunks(32, 0, f->n_pad);
+      long long grid = (long long)f->dd_grid * f->dd_ctas;
+      if (grid > dp.total_chunks) grid = dp.total_chunks;
+      ekf_downdate_kernel<32, false><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
+    }
     f->launches++;
     CK(f, cudaGetLastError());
   }

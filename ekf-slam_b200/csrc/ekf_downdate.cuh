@@ -34,10 +34,12 @@
 
 namespace ekf {
 
-constexpr int kDdComputeWarps = 8;
-constexpr int kDdComputeThreads = kDdComputeWarps * 32;
-constexpr int kDdThreads = kDdComputeThreads + 32;  // + one producer warp
 constexpr int kDdVStages = 3;
+// Two shapes of the same kernel (template parameters CR = rows per chunk, PF = register prefetch):
+//   <64, true >  8 compute warps + producer, 1 CTA / SM, next chunk prefetched into registers
+//   <32, false>  4 compute warps + producer, 3 CTAs / SM, no register double buffer: the load latency
+//                of one CTA is covered by the DMMA phases of the other two (they drift apart freely)
+constexpr int dd_threads(int chunk_rows) { return (chunk_rows / 8) * 32 + 32; }
 
 struct DdParams {
   double *sigma;
@@ -46,6 +48,7 @@ struct DdParams {
   int n_pad, kmax, k2;       // k2 = panel columns in use, a multiple of 4
   int row_begin, row_end;    // rows handled by this launch (multiples of 64); whole matrix: 0, n_pad
   long long total_chunks;
+  int prefetch_ahead;        // L2 prefetch distance of the producer warp, in chunks (0 = off)
 };
 
 // ---- PTX helpers -----------------------------------------------------------------------------
@@ -83,6 +86,11 @@ __device__ __forceinline__ void bulk_s2g(void *dst_gmem, const void *src_smem, u
                "r"(bytes)
                : "memory");
 }
+// L2 prefetch of a contiguous byte range (SASS: UBLKPF): turns the HBM latency of the compute warps'
+// 256-bit Sigma loads into an L2 hit a few chunks later
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
@@ -100,34 +108,33 @@ __device__ __forceinline__ int strip_first_row(int J, int row_begin) {
   const int r = J * EKF_STRIP;
   return r > row_begin ? r : row_begin;
 }
-__host__ __device__ inline long long dd_total_chunks(int n_pad, int row_begin, int row_end) {
+__host__ __device__ inline long long dd_total_chunks(int chunk_rows, int row_begin, int row_end) {
   long long total = 0;
   for (int J = 0; J * EKF_STRIP < row_end; ++J) {
     const int first = J * EKF_STRIP > row_begin ? J * EKF_STRIP : row_begin;
-    total += (row_end - first) / EKF_CHUNK_ROWS;
+    total += (row_end - first) / chunk_rows;
   }
-  (void)n_pad;
   return total;
 }
-__device__ inline ChunkCursor dd_seek(long long c, int row_begin, int row_end) {
+__device__ inline ChunkCursor dd_seek(long long c, int chunk_rows, int row_begin, int row_end) {
   ChunkCursor cur{0, 0};
   for (int J = 0; J * EKF_STRIP < row_end; ++J) {
     const int first = strip_first_row(J, row_begin);
-    const long long here = (row_end - first) / EKF_CHUNK_ROWS;
-    if (c < here) { cur.J = J; cur.row = first + (int)c * EKF_CHUNK_ROWS; return cur; }
+    const long long here = (row_end - first) / chunk_rows;
+    if (c < here) { cur.J = J; cur.row = first + (int)c * chunk_rows; return cur; }
     c -= here;
   }
   cur.J = -1;
   return cur;
 }
-__device__ __forceinline__ void dd_advance(ChunkCursor &cur, int row_begin, int row_end) {
-  cur.row += EKF_CHUNK_ROWS;
+__device__ __forceinline__ void dd_advance(ChunkCursor &cur, int chunk_rows, int row_begin, int row_end) {
+  cur.row += chunk_rows;
   if (cur.row >= row_end) { cur.J += 1; cur.row = strip_first_row(cur.J, row_begin); }
 }
 
 // Shared-memory carve-up (dynamic): [V-row stages][W strip rows][mbarriers]
-__host__ __device__ inline size_t dd_smem_bytes(int k2) {
-  return (size_t)kDdVStages * 2 * k2 * EKF_PBLK * 8           // V rows of the chunk: 2 blocks of 32 rows
+__host__ __device__ inline size_t dd_smem_bytes(int chunk_rows, int k2) {
+  return (size_t)kDdVStages * (chunk_rows / EKF_PBLK) * k2 * EKF_PBLK * 8   // V rows of the chunk
          + (size_t)4 * k2 * EKF_PBLK * 8                       // W rows of the strip: 4 blocks of 32 rows
          + 128;                                                // mbarriers
 }
@@ -146,12 +153,16 @@ __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double
 }
 
 // k2 must be a multiple of 4 (the sequential kernel zero-fills the pad columns of an odd scan).
-__global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdParams p) {
+template <int CR, bool PF>
+__global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kernel(const DdParams p) {
+  constexpr int kComputeWarps = CR / 8;            // each warp owns a 32 x 32 tile of the chunk
+  constexpr int kComputeThreads = kComputeWarps * 32;
+  constexpr int kVBlocks = CR / EKF_PBLK;          // 32-row panel blocks per chunk
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int k2 = p.k2;
   const int blk_elems = k2 * EKF_PBLK;  // doubles per 32-row panel block in use
   double *s_v = reinterpret_cast<double *>(smem_raw);
-  double *s_w = s_v + kDdVStages * 2 * blk_elems;
+  double *s_w = s_v + kDdVStages * kVBlocks * blk_elems;
   uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_w + 4 * blk_elems);
   uint64_t *full = s_bar;                  // [kDdVStages] V rows of the chunk landed
   uint64_t *done = s_bar + kDdVStages;     // [kDdVStages] compute warps finished with the stage
@@ -164,7 +175,7 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
   const int n_chunks = (int)(c_end - c_begin);
 
   if (tid == 0) {
-    for (int s = 0; s < kDdVStages; ++s) { mbar_init(&full[s], 1); mbar_init(&done[s], kDdComputeWarps); }
+    for (int s = 0; s < kDdVStages; ++s) { mbar_init(&full[s], 1); mbar_init(&done[s], kComputeWarps); }
     mbar_init(wfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -173,18 +184,30 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
 
   const uint32_t blk_bytes = (uint32_t)blk_elems * 8;
 
-  if (warp == kDdComputeWarps) {
+  if (warp == kComputeWarps) {
     // ================= producer warp: one elected lane feeds the V-row ring ====================
     if ((tid & 31) == 0) {
-      ChunkCursor ld = dd_seek(c_begin, p.row_begin, p.row_end);
+      ChunkCursor ld = dd_seek(c_begin, CR, p.row_begin, p.row_end);
+      ChunkCursor pf = ld;       // Sigma chunk to prefetch into L2: `prefetch_ahead` chunks past `ld`
+      constexpr uint32_t kChunkBytes = CR * EKF_STRIP * 8;
+      int pf_it = 0;
       for (int it = 0; it < n_chunks; ++it) {
         const int s = it % kDdVStages;
         if (it >= kDdVStages) mbar_wait(&done[s], ((it / kDdVStages) - 1) & 1);
-        mbar_expect_tx(&full[s], 2 * blk_bytes);
+        for (; p.prefetch_ahead > 0 && pf_it <= it + p.prefetch_ahead && pf_it < n_chunks; ++pf_it) {
+          if (pf_it >= 2) {      // chunks 0 and 1 are fetched by the compute warps right away
+            const double *src = p.sigma + ekf_elem(p.n_pad, pf.row, pf.J * EKF_STRIP);
+            bulk_prefetch_l2(src, kChunkBytes);
+          }
+          dd_advance(pf, CR, p.row_begin, p.row_end);
+        }
+        mbar_expect_tx(&full[s], kVBlocks * blk_bytes);
         const int vb = ld.row / EKF_PBLK;
-        bulk_g2s(s_v + (s * 2 + 0) * blk_elems, p.V + (int64_t)vb * p.kmax * EKF_PBLK, blk_bytes, &full[s]);
-        bulk_g2s(s_v + (s * 2 + 1) * blk_elems, p.V + (int64_t)(vb + 1) * p.kmax * EKF_PBLK, blk_bytes, &full[s]);
-        dd_advance(ld, p.row_begin, p.row_end);
+#pragma unroll
+        for (int b = 0; b < kVBlocks; ++b)
+          bulk_g2s(s_v + (s * kVBlocks + b) * blk_elems, p.V + (int64_t)(vb + b) * p.kmax * EKF_PBLK, blk_bytes,
+                   &full[s]);
+        dd_advance(ld, CR, p.row_begin, p.row_end);
       }
     }
     return;
@@ -192,7 +215,7 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
 
   // ======================= compute warps ============================================================
   const int lane = tid & 31;
-  const int wr = warp >> 2;        // 32-row block of the chunk (0..1)
+  const int wr = warp >> 2;        // 32-row block of the chunk
   const int wc = warp & 3;         // 32-column block of the strip (0..3)
   const int g = lane >> 2;         // fragment row / column group (0..7)
   const int t4 = lane & 3;         // fragment k index / column pair (0..3)
@@ -203,9 +226,9 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
   for (int i = 0; i < 4; ++i)
     toff[i] = (32 * wr + ekf_panel_row_of_slot(8 * i + g)) * EKF_STRIP + 32 * wc + 4 * t4;
 
-  ChunkCursor cur = dd_seek(c_begin, p.row_begin, p.row_end);
-  double c[4][4][2], cn[4][4][2];
-  {
+  ChunkCursor cur = dd_seek(c_begin, CR, p.row_begin, p.row_end);
+  double c[4][4][2], cn[PF ? 4 : 1][4][2];
+  if (PF) {
     const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -220,18 +243,27 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
     const int s = it % kDdVStages;
     double *out = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
     const int curJ = cur.J;
-    dd_advance(cur, p.row_begin, p.row_end);
-    if (it + 1 < n_chunks) {       // prefetch the next chunk's tile into the second register set
-      const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+    dd_advance(cur, CR, p.row_begin, p.row_end);
+    if (PF) {
+      if (it + 1 < n_chunks) {       // prefetch the next chunk's tile into the second register set
+        const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+            ld256(base + toff[i] + 16 * jj, cn[i][2 * jj][0], cn[i][2 * jj][1], cn[i][2 * jj + 1][0],
+                  cn[i][2 * jj + 1][1]);
+      }
+    } else {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj)
-          ld256(base + toff[i] + 16 * jj, cn[i][2 * jj][0], cn[i][2 * jj][1], cn[i][2 * jj + 1][0], cn[i][2 * jj + 1][1]);
+          ld256(out + toff[i] + 16 * jj, c[i][2 * jj][0], c[i][2 * jj][1], c[i][2 * jj + 1][0], c[i][2 * jj + 1][1]);
     }
     if (curJ != loadedJ) {
       // new strip: all compute warps must be done with the old W rows before they are replaced
-      named_bar_sync(1, kDdComputeThreads);
+      named_bar_sync(1, kComputeThreads);
       if (tid == 0) {
         mbar_expect_tx(wfull, 4 * blk_bytes);
         for (int b = 0; b < 4; ++b)
@@ -243,7 +275,7 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
     }
     mbar_wait(&full[s], (it / kDdVStages) & 1);
 
-    const double *va = s_v + (s * 2 + wr) * blk_elems + lane;
+    const double *va = s_v + (s * kVBlocks + wr) * blk_elems + lane;
     const double *wb = s_w + wc * blk_elems + lane;
 #pragma unroll 2
     for (int ks = 0; ks < ksteps; ++ks) {
@@ -265,10 +297,12 @@ __global__ void __launch_bounds__(kDdThreads, 1) ekf_downdate_kernel(const DdPar
 #pragma unroll
       for (int jj = 0; jj < 2; ++jj)
         st256(out + toff[i] + 16 * jj, c[i][2 * jj][0], c[i][2 * jj][1], c[i][2 * jj + 1][0], c[i][2 * jj + 1][1]);
+    if (PF) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) { c[i][j][0] = cn[i][j][0]; c[i][j][1] = cn[i][j][1]; }
+        for (int j = 0; j < 4; ++j) { c[i][j][0] = cn[i][j][0]; c[i][j][1] = cn[i][j][1]; }
+    }
   }
 }
 
