@@ -91,6 +91,22 @@ def load() -> C.CDLL:
         "ekf_launch_count": (C.c_int, [vp, i64p]),
         "ekf_read_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),
         "ekf_enable_timing": (C.c_int, [vp, i32]),
+        "ekf_batch_create": (C.c_int, [C.POINTER(EkfConfig), i32, C.POINTER(vp)]),
+        "ekf_batch_destroy": (C.c_int, [vp]),
+        "ekf_batch_set_stream": (C.c_int, [vp, vp]),
+        "ekf_batch_synchronize": (C.c_int, [vp]),
+        "ekf_batch_step": (C.c_int, [vp, dp, i32, dp, ip, ip, ip, ip, dp]),
+        "ekf_batch_step_dev": (C.c_int, [vp, vp, i32, vp, vp, vp, vp, vp, vp]),
+        "ekf_batch_last_status": (C.c_int, [vp]),
+        "ekf_batch_launch_count": (C.c_int, [vp, i64p]),
+        "ekf_batch_get_state": (C.c_int, [vp, i32, dp, i32]),
+        "ekf_batch_get_sigma": (C.c_int, [vp, i32, dp]),
+        "ekf_batch_get_count": (C.c_int, [vp, i32, ip]),
+        "ekf_batch_set_state": (C.c_int, [vp, i32, dp, i32]),
+        "ekf_batch_set_sigma": (C.c_int, [vp, i32, dp]),
+        "ekf_batch_set_count": (C.c_int, [vp, i32, i32]),
+        "ekf_batch_set_previous_xy": (C.c_int, [vp, i32, C.c_double, C.c_double]),
+        "ekf_batch_step_bytes": (C.c_int, [vp, i32, i64p]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(L, name)
@@ -293,3 +309,121 @@ class EkfSlam:
         self._check(self._L.ekf_read_timing(self._h, a.ctypes.data_as(fp), b.ctypes.data_as(fp), max_scans,
                                             C.byref(n)), "ekf_read_timing")
         return a[:n.value].astype(np.float64), b[:n.value].astype(np.float64)
+
+
+class EkfBatch:
+    """B independent small filters on one B200, one CTA each (BASELINE config 3).  Mirrors the
+    ekf_batch_* entry points; per filter the semantics are those of EkfSlam.scan."""
+
+    def __init__(self, n_filters: int, n_landmarks: int = 20, q_noise: float = 1.0e-2, r_noise: float = 1.0e-2,
+                 mah_threshold: float = 2.0, prior: float = 10e6, device: int = -1):
+        self._L = load()
+        cfg = EkfConfig()
+        self._L.ekf_default_config(C.byref(cfg))
+        cfg.n_landmarks, cfg.q_noise, cfg.r_noise = n_landmarks, q_noise, r_noise
+        cfg.mah_threshold, cfg.prior, cfg.device = mah_threshold, prior, device
+        h = C.c_void_p()
+        rc = self._L.ekf_batch_create(C.byref(cfg), n_filters, C.byref(h))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_batch_create")
+        self._h = h
+        self.n_filters, self.n_landmarks, self.n = n_filters, n_landmarks, 3 + 2 * n_landmarks
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ekf_batch_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc, where, allow=()):
+        if rc != EKF_OK and rc not in allow:
+            raise EkfError(rc, where)
+        return rc
+
+    def set_stream(self, cuda_stream_ptr: int):
+        self._check(self._L.ekf_batch_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "ekf_batch_set_stream")
+
+    def synchronize(self):
+        self._check(self._L.ekf_batch_synchronize(self._h), "ekf_batch_synchronize")
+
+    def last_status(self) -> int:
+        return self._L.ekf_batch_last_status(self._h)
+
+    def step(self, poses, xy, ids=None, m_count=None, allow=()):
+        """poses [B,3] (theta, x, y); xy [B,m,2]; ids [B,m] or None; m_count [B] or None.
+        Returns (assoc [B,m], count [B], pose_after [B,3])."""
+        B = self.n_filters
+        poses = np.ascontiguousarray(poses, dtype=np.float64).reshape(B, 3)
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(B, -1, 2)
+        m = xy.shape[1]
+        idp = mcp = None
+        if ids is not None:
+            ids = np.ascontiguousarray(ids, dtype=np.int32).reshape(B, m)
+            idp = _ip(ids)
+        if m_count is not None:
+            m_count = np.ascontiguousarray(m_count, dtype=np.int32).reshape(B)
+            mcp = _ip(m_count)
+        assoc = np.full((B, m), -7, dtype=np.int32)
+        cnt = np.zeros(B, dtype=np.int32)
+        pose = np.zeros((B, 3))
+        self._check(self._L.ekf_batch_step(self._h, _dp(poses), m, _dp(xy), idp, mcp, _ip(assoc), _ip(cnt),
+                                           _dp(pose)), "ekf_batch_step", allow)
+        return assoc, cnt, pose
+
+    def step_dev(self, poses_ptr: int, m: int, xy_ptr: int, ids_ptr: int = 0, m_count_ptr: int = 0,
+                 assoc_ptr: int = 0, count_ptr: int = 0, pose_ptr: int = 0):
+        vp = C.c_void_p
+        self._check(self._L.ekf_batch_step_dev(self._h, vp(poses_ptr), m, vp(xy_ptr), vp(ids_ptr or None),
+                                               vp(m_count_ptr or None), vp(assoc_ptr or None),
+                                               vp(count_ptr or None), vp(pose_ptr or None)), "ekf_batch_step_dev")
+
+    def state(self, index: int) -> np.ndarray:
+        out = np.zeros(self.n)
+        self._check(self._L.ekf_batch_get_state(self._h, index, _dp(out), self.n), "ekf_batch_get_state")
+        return out
+
+    def sigma(self, index: int) -> np.ndarray:
+        out = np.zeros((self.n, self.n))
+        self._check(self._L.ekf_batch_get_sigma(self._h, index, _dp(out)), "ekf_batch_get_sigma")
+        return out
+
+    def count(self, index: int) -> int:
+        c = C.c_int32(0)
+        self._check(self._L.ekf_batch_get_count(self._h, index, C.byref(c)), "ekf_batch_get_count")
+        return int(c.value)
+
+    def set_state(self, index: int, values):
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        self._check(self._L.ekf_batch_set_state(self._h, index, _dp(values), len(values)), "ekf_batch_set_state")
+
+    def set_sigma(self, index: int, full):
+        full = np.ascontiguousarray(full, dtype=np.float64)
+        self._check(self._L.ekf_batch_set_sigma(self._h, index, _dp(full)), "ekf_batch_set_sigma")
+
+    def set_count(self, index: int, count: int):
+        self._check(self._L.ekf_batch_set_count(self._h, index, int(count)), "ekf_batch_set_count")
+
+    def set_previous_xy(self, index: int, x: float, y: float):
+        self._check(self._L.ekf_batch_set_previous_xy(self._h, index, float(x), float(y)),
+                    "ekf_batch_set_previous_xy")
+
+    def step_bytes(self, m: int) -> int:
+        a = C.c_int64(0)
+        self._check(self._L.ekf_batch_step_bytes(self._h, m, C.byref(a)), "ekf_batch_step_bytes")
+        return int(a.value)
+
+    def launch_count(self) -> int:
+        a = C.c_int64(0)
+        self._check(self._L.ekf_batch_launch_count(self._h, C.byref(a)), "ekf_batch_launch_count")
+        return int(a.value)

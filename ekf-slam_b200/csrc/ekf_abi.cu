@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../../include/ekf_slam_b200.h"
+#include "ekf_batch.cuh"
 #include "ekf_downdate.cuh"
 #include "ekf_layout.h"
 #include "ekf_seq.cuh"
@@ -143,3 +144,4 @@ int env_int(const char *name, int dflt) {
 #include "ekf_abi_lifetime.inl"
 #include "ekf_abi_scan.inl"
 #include "ekf_abi_access.inl"
+#include "ekf_abi_batch.inl"

@@ -1,0 +1,295 @@
+// Part of ekf_abi.cu: batched mode (B independent small filters, ekf_batch.cuh).
+
+struct ekf_batch {
+  ekf_config cfg{};
+  int device = 0;
+  int B = 0, N = 0, n = 0, tri = 0;
+  double *sigma = nullptr, *mu = nullptr, *prev = nullptr;
+  int *cnt = nullptr, *status = nullptr;
+  // staging for the host-pointer step
+  unsigned char *io_dev = nullptr, *io_host = nullptr, *res_dev = nullptr, *res_host = nullptr;
+  size_t io_cap = 0, res_cap = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  int64_t launches = 0;
+  int latched = EKF_OK;
+};
+
+namespace {
+
+#define CKB(b, call)                                                               \
+  do {                                                                             \
+    cudaError_t e_ = (call);                                                       \
+    if (e_ != cudaSuccess) {                                                       \
+      fprintf(stderr, "ekf_batch: %s: %s\n", #call, cudaGetErrorString(e_));       \
+      (b)->latched = EKF_ERR_CUDA;                                                 \
+      return EKF_ERR_CUDA;                                                         \
+    }                                                                              \
+  } while (0)
+
+int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, const int32_t *ids,
+                 const int32_t *m_count, int32_t *assoc, int32_t *count, double *pose_out) {
+  BatchParams p{};
+  p.B = b->B; p.N = b->N; p.n = b->n; p.tri = b->tri;
+  p.q_noise = b->cfg.q_noise; p.r_noise = b->cfg.r_noise; p.thr = b->cfg.mah_threshold;
+  p.sigma = b->sigma; p.mu = b->mu; p.prev = b->prev; p.cnt = b->cnt; p.status = b->status;
+  p.pose = poses; p.xy = xy; p.ids = ids; p.m_count = m_count; p.m = m;
+  p.assoc_out = assoc; p.cnt_out = count; p.pose_out = pose_out;
+  ekf_batch_kernel<<<b->B, kBatchThreads, batch_smem_bytes(b->n), b->stream>>>(p);
+  b->launches++;
+  CKB(b, cudaGetLastError());
+  return EKF_OK;
+}
+
+struct BatchIo {
+  size_t pose, xy, ids, mc, total;
+  size_t r_assoc, r_cnt, r_pose, r_status, r_total;
+  BatchIo(int B, int m) {
+    pose = 0; xy = align_up((size_t)24 * B, 16); ids = xy + (size_t)16 * B * m;
+    mc = ids + (size_t)4 * B * m; total = align_up(mc + (size_t)4 * B, 16);
+    r_pose = 0; r_assoc = align_up((size_t)24 * B, 16); r_cnt = r_assoc + (size_t)4 * B * m;
+    r_status = r_cnt + (size_t)4 * B; r_total = align_up(r_status + 4, 16);
+  }
+};
+
+int batch_ensure_io(ekf_batch *b, int m) {
+  const BatchIo io(b->B, m);
+  if (io.total > b->io_cap) {
+    if (b->io_dev) cudaFree(b->io_dev);
+    if (b->io_host) cudaFreeHost(b->io_host);
+    b->io_dev = b->io_host = nullptr; b->io_cap = 0;
+    CKB(b, cudaMalloc(&b->io_dev, io.total));
+    CKB(b, cudaMallocHost(&b->io_host, io.total));
+    b->io_cap = io.total;
+  }
+  if (io.r_total > b->res_cap) {
+    if (b->res_dev) cudaFree(b->res_dev);
+    if (b->res_host) cudaFreeHost(b->res_host);
+    b->res_dev = b->res_host = nullptr; b->res_cap = 0;
+    CKB(b, cudaMalloc(&b->res_dev, io.r_total));
+    CKB(b, cudaMallocHost(&b->res_host, io.r_total));
+    b->res_cap = io.r_total;
+  }
+  return EKF_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ekf_batch_destroy(ekf_batch *b) {
+  if (!b) return EKF_ERR_INVALID;
+  {
+    DeviceGuard guard(b->device);
+    if (b->stream) cudaStreamSynchronize(b->stream);
+    cudaFree(b->sigma); cudaFree(b->mu); cudaFree(b->prev); cudaFree(b->cnt); cudaFree(b->status);
+    cudaFree(b->io_dev); cudaFree(b->res_dev);
+    if (b->io_host) cudaFreeHost(b->io_host);
+    if (b->res_host) cudaFreeHost(b->res_host);
+    if (b->own_stream) cudaStreamDestroy(b->own_stream);
+  }
+  delete b;
+  return EKF_OK;
+}
+
+int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) {
+  if (!cfg || !out || n_filters < 1) return EKF_ERR_INVALID;
+  *out = nullptr;
+  if (cfg->n_landmarks < 1 || 3 + 2 * cfg->n_landmarks > 131) return EKF_ERR_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return EKF_ERR_NO_DEVICE;
+  int dev = cfg->device;
+  if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) return EKF_ERR_NO_DEVICE;
+  if (dev >= ndev) return EKF_ERR_INVALID;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess || prop.major < 10) return EKF_ERR_NO_DEVICE;
+  ekf_batch *b = new (std::nothrow) ekf_batch();
+  if (!b) return EKF_ERR_NOMEM;
+  b->cfg = *cfg; b->device = dev; b->B = n_filters; b->N = cfg->n_landmarks;
+  b->n = 3 + 2 * b->N; b->tri = b->n * (b->n + 1) / 2;
+  DeviceGuard guard(dev);
+  auto fail = [&](cudaError_t e, const char *what) {
+    fprintf(stderr, "ekf_batch_create: %s: %s\n", what, cudaGetErrorString(e));
+    ekf_batch_destroy(b);
+    return e == cudaErrorMemoryAllocation ? EKF_ERR_NOMEM : EKF_ERR_CUDA;
+  };
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(e_, #call); } while (0)
+  CKC(cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking));
+  b->stream = b->own_stream;
+  const size_t sig_bytes = (size_t)b->B * b->tri * sizeof(double);
+  CKC(cudaMalloc(&b->sigma, sig_bytes));
+  CKC(cudaMalloc(&b->mu, (size_t)b->B * b->n * sizeof(double)));
+  CKC(cudaMalloc(&b->prev, (size_t)b->B * 2 * sizeof(double)));
+  CKC(cudaMalloc(&b->cnt, (size_t)b->B * sizeof(int)));
+  CKC(cudaMalloc(&b->status, sizeof(int)));
+  CKC(cudaMemsetAsync(b->sigma, 0, sig_bytes, b->stream));
+  CKC(cudaMemsetAsync(b->mu, 0, (size_t)b->B * b->n * sizeof(double), b->stream));
+  CKC(cudaMemsetAsync(b->prev, 0, (size_t)b->B * 2 * sizeof(double), b->stream));
+  CKC(cudaMemsetAsync(b->cnt, 0, (size_t)b->B * sizeof(int), b->stream));
+  CKC(cudaMemsetAsync(b->status, 0, sizeof(int), b->stream));
+  batch_init_prior_kernel<<<(unsigned)(((size_t)b->B * b->n + 255) / 256), 256, 0, b->stream>>>(
+      b->sigma, b->B, b->n, b->tri, cfg->prior);   // slam.cpp:128-132
+  b->launches++;
+  CKC(cudaGetLastError());
+  CKC(cudaFuncSetAttribute(ekf_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)batch_smem_bytes(131)));
+  CKC(cudaFuncSetAttribute(ekf_batch_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                           cudaSharedmemCarveoutMaxShared));
+  CKC(cudaStreamSynchronize(b->stream));
+#undef CKC
+  *out = b;
+  return EKF_OK;
+}
+
+int ekf_batch_set_stream(ekf_batch *b, void *cuda_stream) {
+  if (!b) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  b->stream = cuda_stream ? (cudaStream_t)cuda_stream : b->own_stream;
+  return EKF_OK;
+}
+
+int ekf_batch_synchronize(ekf_batch *b) {
+  if (!b) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  return EKF_OK;
+}
+
+int ekf_batch_last_status(ekf_batch *b) {
+  if (!b) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  int dev_status = 0;
+  CKB(b, cudaMemcpyAsync(&dev_status, b->status, sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+  CKB(b, cudaMemsetAsync(b->status, 0, sizeof(int), b->stream));
+  CKB(b, cudaStreamSynchronize(b->stream));
+  const int s = b->latched != EKF_OK ? b->latched : dev_status;
+  b->latched = EKF_OK;
+  return s;
+}
+
+int ekf_batch_launch_count(ekf_batch *b, int64_t *launches) {
+  if (!b || !launches) return EKF_ERR_INVALID;
+  *launches = b->launches;
+  return EKF_OK;
+}
+
+int ekf_batch_step_bytes(ekf_batch *b, int32_t m, int64_t *bytes) {
+  if (!b || !bytes || m < 0) return EKF_ERR_INVALID;
+  *bytes = 8LL * b->n * (b->n + 1) + 16LL * b->n + 16LL * m + 24;
+  return EKF_OK;
+}
+
+int ekf_batch_step_dev(ekf_batch *b, const double *poses_dev, int32_t m, const double *xy_dev,
+                       const int32_t *ids_dev, const int32_t *m_count_dev, int32_t *assoc_dev,
+                       int32_t *count_dev, double *pose_dev) {
+  if (!b || m < 0 || !poses_dev) return EKF_ERR_INVALID;
+  if (m == 0) return EKF_ERR_EMPTY_SCAN;
+  if (!xy_dev) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  return batch_launch(b, poses_dev, m, xy_dev, ids_dev, m_count_dev, assoc_dev, count_dev, pose_dev);
+}
+
+int ekf_batch_step(ekf_batch *b, const double *poses, int32_t m, const double *xy, const int32_t *ids,
+                   const int32_t *m_count, int32_t *out_assoc, int32_t *out_count, double *out_pose) {
+  if (!b || m < 0 || !poses) return EKF_ERR_INVALID;
+  if (m == 0) return EKF_ERR_EMPTY_SCAN;
+  if (!xy) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  int rc = batch_ensure_io(b, m);
+  if (rc != EKF_OK) return rc;
+  const BatchIo io(b->B, m);
+  const size_t B = (size_t)b->B;
+  memcpy(b->io_host + io.pose, poses, 24 * B);
+  memcpy(b->io_host + io.xy, xy, 16 * B * m);
+  if (ids) memcpy(b->io_host + io.ids, ids, 4 * B * m);
+  if (m_count) memcpy(b->io_host + io.mc, m_count, 4 * B);
+  CKB(b, cudaMemcpyAsync(b->io_dev, b->io_host, io.total, cudaMemcpyHostToDevice, b->stream));
+  rc = batch_launch(b, reinterpret_cast<const double *>(b->io_dev + io.pose), m,
+                    reinterpret_cast<const double *>(b->io_dev + io.xy),
+                    ids ? reinterpret_cast<const int32_t *>(b->io_dev + io.ids) : nullptr,
+                    m_count ? reinterpret_cast<const int32_t *>(b->io_dev + io.mc) : nullptr,
+                    reinterpret_cast<int32_t *>(b->res_dev + io.r_assoc),
+                    reinterpret_cast<int32_t *>(b->res_dev + io.r_cnt),
+                    reinterpret_cast<double *>(b->res_dev + io.r_pose));
+  if (rc != EKF_OK) return rc;
+  CKB(b, cudaMemcpyAsync(b->res_dev + io.r_status, b->status, sizeof(int), cudaMemcpyDeviceToDevice, b->stream));
+  CKB(b, cudaMemsetAsync(b->status, 0, sizeof(int), b->stream));
+  CKB(b, cudaMemcpyAsync(b->res_host, b->res_dev, io.r_total, cudaMemcpyDeviceToHost, b->stream));
+  CKB(b, cudaStreamSynchronize(b->stream));
+  if (out_assoc) memcpy(out_assoc, b->res_host + io.r_assoc, 4 * B * m);
+  if (out_count) memcpy(out_count, b->res_host + io.r_cnt, 4 * B);
+  if (out_pose) memcpy(out_pose, b->res_host + io.r_pose, 24 * B);
+  int dev_status = 0;
+  memcpy(&dev_status, b->res_host + io.r_status, 4);
+  return dev_status;
+}
+
+// ---- accessors / fixtures (host-side pack / unpack of one filter; never on the timed path) ----
+int ekf_batch_get_state(ekf_batch *b, int32_t index, double *out, int32_t n) {
+  if (!b || !out || index < 0 || index >= b->B || n < 0 || n > b->n) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  CKB(b, cudaMemcpy(out, b->mu + (size_t)index * b->n, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+  return EKF_OK;
+}
+
+int ekf_batch_set_state(ekf_batch *b, int32_t index, const double *in, int32_t n) {
+  if (!b || !in || index < 0 || index >= b->B || n < 0 || n > b->n) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  CKB(b, cudaMemcpy(b->mu + (size_t)index * b->n, in, (size_t)n * sizeof(double), cudaMemcpyHostToDevice));
+  return EKF_OK;
+}
+
+int ekf_batch_get_sigma(ekf_batch *b, int32_t index, double *out) {
+  if (!b || !out || index < 0 || index >= b->B) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  std::vector<double> tri((size_t)b->tri);
+  CKB(b, cudaMemcpy(tri.data(), b->sigma + (size_t)index * b->tri, tri.size() * sizeof(double),
+                    cudaMemcpyDeviceToHost));
+  const int n = b->n;
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j <= i; ++j) out[(size_t)i * n + j] = out[(size_t)j * n + i] = tri[(size_t)i * (i + 1) / 2 + j];
+  return EKF_OK;
+}
+
+int ekf_batch_set_sigma(ekf_batch *b, int32_t index, const double *in) {
+  if (!b || !in || index < 0 || index >= b->B) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  std::vector<double> tri((size_t)b->tri);
+  const int n = b->n;
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j <= i; ++j) tri[(size_t)i * (i + 1) / 2 + j] = in[(size_t)i * n + j];
+  CKB(b, cudaMemcpy(b->sigma + (size_t)index * b->tri, tri.data(), tri.size() * sizeof(double),
+                    cudaMemcpyHostToDevice));
+  return EKF_OK;
+}
+
+int ekf_batch_get_count(ekf_batch *b, int32_t index, int32_t *count) {
+  if (!b || !count || index < 0 || index >= b->B) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  CKB(b, cudaMemcpy(count, b->cnt + index, sizeof(int), cudaMemcpyDeviceToHost));
+  return EKF_OK;
+}
+
+int ekf_batch_set_count(ekf_batch *b, int32_t index, int32_t count) {
+  if (!b || index < 0 || index >= b->B || count < 0 || count > b->N) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  CKB(b, cudaMemcpy(b->cnt + index, &count, sizeof(int), cudaMemcpyHostToDevice));
+  return EKF_OK;
+}
+
+int ekf_batch_set_previous_xy(ekf_batch *b, int32_t index, double x, double y) {
+  if (!b || index < 0 || index >= b->B) return EKF_ERR_INVALID;
+  DeviceGuard guard(b->device);
+  CKB(b, cudaStreamSynchronize(b->stream));
+  const double v[2] = {x, y};
+  CKB(b, cudaMemcpy(b->prev + 2 * (size_t)index, v, sizeof(v), cudaMemcpyHostToDevice));
+  return EKF_OK;
+}
+
+}  // extern "C"

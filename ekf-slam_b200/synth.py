@@ -139,3 +139,36 @@ class MapHost:
     def after_update(self, filter_pose_theta_xy, odom):
         th, x, y = filter_pose_theta_xy
         self.t_map_odom = _compose((x, y, th), _inverse(odom))   # slam.cpp:273-277
+
+
+# ---- batched Monte-Carlo workload (BASELINE config 3), vectorised over the filters ---------------
+def batch_fields(n_filters, n_landmarks=20, seed=0, pitch=0.9, jitter=0.15):
+    """[B, N, 2] landmark fields: a jittered grid around the origin (separation >= pitch - 2*jitter),
+    a different field per filter."""
+    rng = np.random.default_rng(seed)
+    w = int(math.ceil(math.sqrt(n_landmarks)))
+    k = np.arange(n_landmarks)
+    gx = (k % w - (w - 1) / 2.0) * pitch + 0.37
+    gy = (k // w - (math.ceil(n_landmarks / w) - 1) / 2.0) * pitch + 0.29
+    base = np.stack([gx, gy], axis=1)[None]
+    return base + rng.uniform(-jitter, jitter, size=(n_filters, n_landmarks, 2))
+
+
+def batch_pose(n_filters, step, radius=0.25, dtheta=0.05):
+    """[B, 3] (theta, x, y): every robot drives a small circle, phase-shifted per filter."""
+    ph = dtheta * step + 0.001 * np.arange(n_filters)
+    return np.stack([ph + math.pi / 2, radius * np.cos(ph), radius * np.sin(ph)], axis=1)
+
+
+def batch_scan(fields, poses, rng, m=None, sensor_std=0.001):
+    """Body-frame sightings [B, m, 2] of m landmarks per filter (a random subset and order per
+    filter, nusim.cpp:325-340), and the true ids [B, m]."""
+    B, N, _ = fields.shape
+    m = N if m is None else m
+    order = np.argsort(rng.random((B, N)), axis=1)[:, :m].astype(np.int32)
+    lm = np.take_along_axis(fields, order[:, :, None].astype(np.int64), axis=1)
+    th, x, y = poses[:, 0:1], poses[:, 1:2], poses[:, 2:3]
+    dx, dy = lm[:, :, 0] - x, lm[:, :, 1] - y
+    c, s = np.cos(th), np.sin(th)
+    xy = np.stack([c * dx + s * dy, -s * dx + c * dy], axis=2) + rng.normal(0.0, sensor_std, (B, m, 2))
+    return xy, order

