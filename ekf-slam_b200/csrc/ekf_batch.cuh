@@ -193,12 +193,17 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
       mu[i] = v;
     }
     __syncwarp();
-    for (int i = 0; i < n; ++i) {                              // Sigma -= K G^T on the stored triangle
-      const double2 ki = K[i];
-      const int r = i * (i + 1) / 2;
-      for (int c = lane; c <= i; c += 32) {
-        const double2 gc = G[c];
-        S[r + c] = S[r + c] - (ki.x * gc.x + ki.y * gc.y);
+    // Sigma -= K G^T on the stored triangle: lane owns the columns c = lane + 32 q (its G[c] stays in
+    // registers), walks the rows i >= c; K[i] is a broadcast load
+    for (int c0 = 0; c0 < n; c0 += 32) {
+      const int c = c0 + lane;
+      const double2 gc = c < n ? G[c] : make_double2(0.0, 0.0);
+      double *sp = S + (c0 * (c0 + 1) / 2 + c);
+#pragma unroll 4
+      for (int i = c0; i < n; ++i) {
+        const double2 ki = K[i];
+        if (c <= i) *sp = *sp - (ki.x * gc.x + ki.y * gc.y);
+        sp += i + 1;
       }
     }
     __syncwarp();
