@@ -91,6 +91,11 @@ def load() -> C.CDLL:
         "ekf_launch_count": (C.c_int, [vp, i64p]),
         "ekf_read_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),
         "ekf_enable_timing": (C.c_int, [vp, i32]),
+        "ekf_shard_info": (C.c_int, [vp, ip, ip, i64p]),
+        "ekf_shard_sync_begin": (C.c_int, [vp, C.POINTER(vp), i64p]),
+        "ekf_shard_sync_finish": (C.c_int, [vp]),
+        "ekf_shard_scan_begin": (C.c_int, [vp, vp, i32, vp, vp, i32, C.POINTER(vp), i64p]),
+        "ekf_shard_scan_finish": (C.c_int, [vp, vp, vp, vp, vp]),
         "ekf_batch_create": (C.c_int, [C.POINTER(EkfConfig), i32, C.POINTER(vp)]),
         "ekf_batch_destroy": (C.c_int, [vp]),
         "ekf_batch_set_stream": (C.c_int, [vp, vp]),
@@ -132,12 +137,15 @@ class EkfSlam:
     error behaviour follow the reference callbacks (nuslam/src/slam.cpp:180-316, 318-530)."""
 
     def __init__(self, n_landmarks: int = 50, q_noise: float = 1.0e-2, r_noise: float = 1.0e-2,
-                 mah_threshold: float = 2.0, prior: float = 10e6, device: int = -1, max_scan: int = 0):
+                 mah_threshold: float = 2.0, prior: float = 10e6, device: int = -1, max_scan: int = 0,
+                 shard_rank: int = 0, shard_count: int = 1):
         self._L = load()
         cfg = EkfConfig()
         self._L.ekf_default_config(C.byref(cfg))
         cfg.n_landmarks, cfg.q_noise, cfg.r_noise = n_landmarks, q_noise, r_noise
         cfg.mah_threshold, cfg.prior, cfg.device, cfg.max_scan = mah_threshold, prior, device, max_scan
+        cfg.shard_rank, cfg.shard_count = shard_rank, shard_count
+        self.shard_rank, self.shard_count = shard_rank, shard_count
         h = C.c_void_p()
         rc = self._L.ekf_create(C.byref(cfg), C.byref(h))
         if rc != EKF_OK:
@@ -286,6 +294,35 @@ class EkfSlam:
 
     def fill_procedural(self, seed: int, count: int, grid_w: int):
         self._check(self._L.ekf_fill_procedural(self._h, C.c_uint64(seed), count, grid_w), "ekf_fill_procedural")
+
+    # -- row-sharded large map (see ekf_slam_b200.shard for the drivers) --------------------------
+    def shard_info(self):
+        """(row_begin, row_end, stored_doubles): internal padded row range this handle stores"""
+        a, b, c = C.c_int32(0), C.c_int32(0), C.c_int64(0)
+        self._check(self._L.ekf_shard_info(self._h, C.byref(a), C.byref(b), C.byref(c)), "ekf_shard_info")
+        return int(a.value), int(b.value), int(c.value)
+
+    def shard_sync_begin(self):
+        ptr, cnt = C.c_void_p(), C.c_int64(0)
+        self._check(self._L.ekf_shard_sync_begin(self._h, C.byref(ptr), C.byref(cnt)), "ekf_shard_sync_begin")
+        return int(ptr.value), int(cnt.value)
+
+    def shard_sync_finish(self):
+        self._check(self._L.ekf_shard_sync_finish(self._h), "ekf_shard_sync_finish")
+
+    def shard_scan_begin(self, pose_ptr: int, m: int, xy_ptr: int, ids_ptr: int = 0, last_round: bool = True):
+        ptr, cnt = C.c_void_p(), C.c_int64(0)
+        vp = C.c_void_p
+        self._check(self._L.ekf_shard_scan_begin(self._h, vp(pose_ptr or None), m, vp(xy_ptr), vp(ids_ptr or None),
+                                                 1 if last_round else 0, C.byref(ptr), C.byref(cnt)),
+                    "ekf_shard_scan_begin")
+        return int(ptr.value), int(cnt.value)
+
+    def shard_scan_finish(self, assoc_ptr: int = 0, done_ptr: int = 0, pose_ptr: int = 0, count_ptr: int = 0):
+        vp = C.c_void_p
+        self._check(self._L.ekf_shard_scan_finish(self._h, vp(assoc_ptr or None), vp(done_ptr or None),
+                                                  vp(pose_ptr or None), vp(count_ptr or None)),
+                    "ekf_shard_scan_finish")
 
     def storage(self):
         a, b = C.c_int64(0), C.c_int64(0)

@@ -16,6 +16,7 @@
 #include "ekf_downdate.cuh"
 #include "ekf_layout.h"
 #include "ekf_seq.cuh"
+#include "ekf_shard.cuh"
 #include "ekf_util.cuh"
 
 using namespace ekf;
@@ -26,6 +27,16 @@ struct ekf_filter {
   int num_sms = 0;
   int N = 0, n = 0, n_int = 0, n_pad = 0, kmax = kMaxK2;
   int64_t sigma_elems = 0;
+  EkfLay lay{0, 0};        // rows of Sigma this handle stores (whole matrix unless row-sharded)
+  bool sharded = false;
+  bool side_valid = false; // sharded: Pp / D replicated and current
+  double *cols = nullptr;  // sharded: exchange buffer, kMaxChunkM x n_pad x 2
+  int *guess = nullptr;    // sharded: speculative association of the round
+  int *done_dev = nullptr; // sharded: measurements processed by the last finish
+  // the round opened by ekf_shard_scan_begin
+  int pend_m = -1, pend_finish = 0;
+  const double *pend_xy = nullptr;
+  const int32_t *pend_ids = nullptr;
   // device storage
   double *sigma = nullptr, *mu = nullptr, *W = nullptr, *V = nullptr;
   double4 *Pp = nullptr, *D = nullptr;
@@ -145,3 +156,4 @@ int env_int(const char *name, int dflt) {
 #include "ekf_abi_scan.inl"
 #include "ekf_abi_access.inl"
 #include "ekf_abi_batch.inl"
+#include "ekf_abi_shard.inl"

@@ -106,7 +106,7 @@ int ekf_get_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
     const size_t bytes = (size_t)(r1 - r) * ld * 8;
     int rc = ensure_scratch(f, bytes);
     if (rc != EKF_OK) return rc;
-    get_block_kernel<<<f->num_sms * 8, 256, 0, f->stream>>>(f->sigma, f->n_pad, r, r1, j0, j1, f->scratch_dev);
+    get_block_kernel<<<f->num_sms * 8, 256, 0, f->stream>>>(f->sigma, f->lay, r, r1, j0, j1, f->scratch_dev);
     f->launches++;
     CK(f, cudaGetLastError());
     CK(f, cudaMemcpyAsync(out + (size_t)(r - i0) * ld, f->scratch_dev, bytes, cudaMemcpyDeviceToHost, f->stream));
@@ -118,6 +118,7 @@ int ekf_get_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
 int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32_t j1, const double *in) {
   if (!block_args_ok(f, i0, i1, j0, j1, in)) return EKF_ERR_INVALID;
   if (i1 == i0 || j1 == j0) return EKF_OK;
+  f->side_valid = false;
   DeviceGuard guard(f->device);
   const size_t ld = (size_t)(j1 - j0);
   size_t rows_per = kBlockPieceBytes / (ld * 8);
@@ -128,7 +129,7 @@ int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
     int rc = ensure_scratch(f, bytes);
     if (rc != EKF_OK) return rc;
     CK(f, cudaMemcpyAsync(f->scratch_dev, in + (size_t)(r - i0) * ld, bytes, cudaMemcpyHostToDevice, f->stream));
-    set_block_kernel<<<f->num_sms * 8, 256, 0, f->stream>>>(f->sigma, f->n_pad, r, r1, j0, j1, f->scratch_dev);
+    set_block_kernel<<<f->num_sms * 8, 256, 0, f->stream>>>(f->sigma, f->lay, r, r1, j0, j1, f->scratch_dev);
     f->launches++;
     CK(f, cudaGetLastError());
     CK(f, cudaStreamSynchronize(f->stream));
@@ -138,8 +139,9 @@ int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
 
 int ekf_fill_procedural(ekf_filter *f, uint64_t seed, int32_t count, int32_t grid_w) {
   if (!f || count < 0 || count > f->N || grid_w < 1) return EKF_ERR_INVALID;
+  f->side_valid = false;
   DeviceGuard guard(f->device);
-  fill_procedural_sigma_kernel<<<f->num_sms * 16, 256, 0, f->stream>>>(f->sigma, f->n_pad, count, seed, f->cfg.prior);
+  fill_procedural_sigma_kernel<<<f->num_sms * 16, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, count, seed, f->cfg.prior);
   fill_procedural_state_kernel<<<(f->N + 255) / 256, 256, 0, f->stream>>>(f->mu, f->n_pad, f->N, count, grid_w, seed);
   f->launches += 2;
   CK(f, cudaGetLastError());

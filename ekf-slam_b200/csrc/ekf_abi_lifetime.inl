@@ -38,7 +38,8 @@ int ekf_destroy(ekf_filter *f) {
     DeviceGuard guard(f->device);
     if (f->stream) cudaStreamSynchronize(f->stream);
     cudaFree(f->sigma); cudaFree(f->mu); cudaFree(f->W); cudaFree(f->V);
-    cudaFree(f->Pp); cudaFree(f->D); cudaFree(f->cnt); cudaFree(f->status);
+    cudaFree(f->Pp); cudaFree(f->cnt); cudaFree(f->status);   // D lives in the Pp allocation
+    cudaFree(f->cols); cudaFree(f->guess); cudaFree(f->done_dev);
     cudaFree(f->prev_xy); cudaFree(f->bar); cudaFree(f->slot_d); cudaFree(f->slot_k); cudaFree(f->slot_rec);
     cudaFree(f->io_dev); cudaFree(f->res_dev); cudaFree(f->scratch_dev);
     if (f->io_host) cudaFreeHost(f->io_host);
@@ -55,7 +56,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   if (!cfg || !out) return EKF_ERR_INVALID;
   *out = nullptr;
   if (cfg->n_landmarks < 1 || cfg->n_landmarks > 500000000) return EKF_ERR_INVALID;
-  if (cfg->shard_count > 1) return EKF_ERR_INVALID;  // row-sharded handles: ekf_shard_* (later)
+  if (cfg->shard_count > 1 && (cfg->shard_rank < 0 || cfg->shard_rank >= cfg->shard_count)) return EKF_ERR_INVALID;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return EKF_ERR_NO_DEVICE;
   int dev = cfg->device;
@@ -74,7 +75,15 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   f->n = 3 + 2 * f->N;
   f->n_int = ekf_n_int(f->N);
   f->n_pad = ekf_n_pad(f->N);
-  f->sigma_elems = ekf_sigma_elems(f->n_pad);
+  f->sharded = cfg->shard_count > 1;
+  f->lay = ekf_lay_full(f->n_pad);
+  if (f->sharded) {
+    if (cfg->shard_count > f->n_pad / EKF_STRIP) return (delete f, EKF_ERR_INVALID);
+    f->lay.rb = ekf_shard_bound(f->n_pad, cfg->shard_rank, cfg->shard_count);
+    f->lay.re = ekf_shard_bound(f->n_pad, cfg->shard_rank + 1, cfg->shard_count);
+    if (f->lay.re <= f->lay.rb) return (delete f, EKF_ERR_INVALID);
+  }
+  f->sigma_elems = ekf_lay_elems(f->lay);
   DeviceGuard guard(dev);
 
   auto fail = [&](cudaError_t e, const char *what) {
@@ -91,8 +100,14 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   CKC(cudaMalloc(&f->mu, (size_t)f->n_pad * sizeof(double)));
   CKC(cudaMalloc(&f->W, panel_bytes));
   CKC(cudaMalloc(&f->V, panel_bytes));
-  CKC(cudaMalloc(&f->Pp, (size_t)f->n_pad * sizeof(double4)));
-  CKC(cudaMalloc(&f->D, (size_t)f->N * sizeof(double4)));
+  // Pp (n_pad rows) and D (N blocks) share one allocation: a sharded handle all-reduces both at once
+  CKC(cudaMalloc(&f->Pp, ((size_t)f->n_pad + f->N) * sizeof(double4)));
+  f->D = f->Pp + f->n_pad;
+  if (f->sharded) {
+    CKC(cudaMalloc(&f->cols, (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double)));
+    CKC(cudaMalloc(&f->guess, kMaxChunkM * sizeof(int)));
+    CKC(cudaMalloc(&f->done_dev, sizeof(int)));
+  }
   CKC(cudaMalloc(&f->cnt, sizeof(int)));
   CKC(cudaMalloc(&f->status, sizeof(int)));
   CKC(cudaMalloc(&f->prev_xy, 2 * sizeof(double)));
@@ -135,13 +150,12 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   CKC(cudaMemsetAsync(f->mu, 0, (size_t)f->n_pad * sizeof(double), f->stream));
   CKC(cudaMemsetAsync(f->W, 0, panel_bytes, f->stream));
   CKC(cudaMemsetAsync(f->V, 0, panel_bytes, f->stream));
-  CKC(cudaMemsetAsync(f->Pp, 0, (size_t)f->n_pad * sizeof(double4), f->stream));
-  CKC(cudaMemsetAsync(f->D, 0, (size_t)f->N * sizeof(double4), f->stream));
+  CKC(cudaMemsetAsync(f->Pp, 0, ((size_t)f->n_pad + f->N) * sizeof(double4), f->stream));
   CKC(cudaMemsetAsync(f->cnt, 0, sizeof(int), f->stream));
   CKC(cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
   CKC(cudaMemsetAsync(f->prev_xy, 0, 2 * sizeof(double), f->stream));
   CKC(cudaMemsetAsync(f->bar, 0, sizeof(unsigned long long), f->stream));
-  init_prior_kernel<<<(2 * f->N + 255) / 256, 256, 0, f->stream>>>(f->sigma, f->n_pad, f->n_int, cfg->prior);
+  init_prior_kernel<<<(2 * f->N + 255) / 256, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_int, cfg->prior);
   f->launches++;
   CKC(cudaGetLastError());
   if (ensure_io(f, cfg->max_scan > 0 ? cfg->max_scan : 64) != EKF_OK) { ekf_destroy(f); return EKF_ERR_CUDA; }

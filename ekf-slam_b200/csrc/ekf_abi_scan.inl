@@ -8,7 +8,8 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
                  const int32_t *ids_dev, const uint8_t *action_dev, int32_t *assoc_dev, int finish,
                  double *pose_out_dev, int *cnt_out_dev) {
   SeqParams sp{};
-  sp.N = f->N; sp.n_pad = f->n_pad; sp.kmax = f->kmax;
+  sp.N = f->N; sp.n_pad = f->n_pad; sp.kmax = f->kmax; sp.lay = f->lay;
+  sp.side_mode = 0; sp.cols = nullptr; sp.guess = nullptr; sp.done_out = nullptr;
   sp.q_noise = f->cfg.q_noise; sp.r_noise = f->cfg.r_noise; sp.thr = f->cfg.mah_threshold;
   sp.sigma = f->sigma; sp.mu = f->mu; sp.Pp = f->Pp; sp.D = f->D; sp.W = f->W; sp.V = f->V;
   sp.cnt = f->cnt; sp.prev_xy = f->prev_xy; sp.status = f->status;
@@ -17,7 +18,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   sp.assoc_out = assoc_dev; sp.pose_out = pose_out_dev; sp.cnt_out = cnt_out_dev;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
-  f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
+  f->bar_base += (unsigned long long)(mc > 0 ? mc : 1) * (unsigned long long)f->seq_grid;
 
   const bool timed = f->ev_cap > 0 && mc > 0;
   const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 3 : 0;
@@ -31,15 +32,15 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
     DdParams dp{};
     dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
     dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;  // whole k-steps; pad columns are zero
-    dp.row_begin = 0; dp.row_end = f->n_pad;
+    dp.lay = f->lay; dp.row_begin = f->lay.rb; dp.row_end = f->lay.re;
     dp.prefetch_ahead = f->dd_prefetch;
     if (f->dd_variant == 0) {
-      dp.total_chunks = dd_total_chunks(64, 0, f->n_pad);
+      dp.total_chunks = dd_total_chunks(64, dp.row_begin, dp.row_end);
       long long grid = f->dd_grid;
       if (grid > dp.total_chunks) grid = dp.total_chunks;
       ekf_downdate_kernel<64, true><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
     } else {
-      dp.total_chunks = dd_total_chunks(32, 0, f->n_pad);
+      dp.total_chunks = dd_total_chunks(32, dp.row_begin, dp.row_end);
       long long grid = (long long)f->dd_grid * f->dd_ctas;
       if (grid > dp.total_chunks) grid = dp.total_chunks;
       ekf_downdate_kernel<32, false><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
@@ -54,6 +55,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
 // One whole scan from device inputs; splits into chunks of kMaxChunkM measurements.
 int scan_device(ekf_filter *f, const double *pose_dev, int m, const double *xy_dev, const int32_t *ids_dev,
                 const uint8_t *action_dev, int32_t *assoc_dev, double *pose_out_dev, int *cnt_out_dev) {
+  if (f->sharded) return EKF_ERR_INVALID;   // a row shard cannot run a scan alone: ekf_shard_scan_*
   int t0 = 0;
   bool first = true;
   do {

@@ -1,0 +1,116 @@
+// Part of ekf_abi.cu: row-sharded single large map (kernels and protocol: ekf_shard.cuh).
+
+namespace {
+
+int shard_ok(ekf_filter *f) { return f && f->sharded; }
+
+}  // namespace
+
+extern "C" {
+
+int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t *stored_doubles) {
+  if (!f) return EKF_ERR_INVALID;
+  if (row_begin) *row_begin = f->lay.rb;
+  if (row_end) *row_end = f->lay.re;
+  if (stored_doubles) *stored_doubles = f->sigma_elems;
+  return EKF_OK;
+}
+
+int ekf_shard_sync_begin(ekf_filter *f, double **xchg_dev, int64_t *xchg_doubles) {
+  if (!shard_ok(f) || !xchg_dev || !xchg_doubles) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  shard_side_extract_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
+  f->launches++;
+  CK(f, cudaGetLastError());
+  *xchg_dev = reinterpret_cast<double *>(f->Pp);
+  *xchg_doubles = 4 * ((int64_t)f->n_pad + f->N);
+  return EKF_OK;
+}
+
+int ekf_shard_sync_finish(ekf_filter *f) {
+  if (!shard_ok(f)) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  shard_side_fix_pose_kernel<<<1, 32, 0, f->stream>>>(f->Pp);
+  f->launches++;
+  CK(f, cudaGetLastError());
+  f->side_valid = true;
+  return EKF_OK;
+}
+
+int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const double *xy_dev,
+                         const int32_t *ids_dev, int32_t last_round, double **xchg_dev, int64_t *xchg_doubles) {
+  if (!shard_ok(f) || m < 1 || !xy_dev || !xchg_dev || !xchg_doubles) return EKF_ERR_INVALID;
+  if (!f->side_valid) return EKF_ERR_INVALID;        // ekf_shard_sync_begin / _finish first
+  DeviceGuard guard(f->device);
+  const int mc = m < kMaxChunkM ? m : kMaxChunkM;    // a round handles at most kMaxChunkM sightings
+  if (pose_dev) {
+    shard_predict_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->Pp, f->mu, pose_dev, f->prev_xy, f->N,
+                                                            f->cfg.q_noise);
+    f->launches++;
+  }
+  shard_guess_kernel<<<mc, kGuessThreads, 0, f->stream>>>(f->Pp, f->D, f->mu, f->cnt, xy_dev, ids_dev, f->guess,
+                                                          f->cfg.r_noise, f->cfg.mah_threshold);
+  // test-only fault injection: forget the speculation for one sighting so that the stop / resume path runs
+  const int drop = env_int("EKF_SHARD_DROP_GUESS", -1);
+  if (drop >= 0 && drop < mc) CK(f, cudaMemsetAsync(f->guess + drop, 0xFF, sizeof(int), f->stream));
+  shard_extract_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc,
+                                                                   f->cols);
+  f->launches += 2;
+  CK(f, cudaGetLastError());
+  f->pend_m = mc; f->pend_xy = xy_dev; f->pend_ids = ids_dev;
+  f->pend_finish = (last_round && mc == m) ? 1 : 0;
+  *xchg_dev = f->cols;
+  *xchg_doubles = (int64_t)mc * f->n_pad * 2;
+  return EKF_OK;
+}
+
+int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, double *pose_out_dev,
+                          int32_t *count_dev) {
+  if (!shard_ok(f) || f->pend_m < 1) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  int rc = ensure_io(f, 1);
+  if (rc != EKF_OK) return rc;
+  const ResLayout res(1);
+  const int mc = f->pend_m;
+  SeqParams sp{};
+  sp.N = f->N; sp.n_pad = f->n_pad; sp.kmax = f->kmax; sp.lay = f->lay;
+  sp.q_noise = f->cfg.q_noise; sp.r_noise = f->cfg.r_noise; sp.thr = f->cfg.mah_threshold;
+  sp.sigma = f->sigma; sp.mu = f->mu; sp.Pp = f->Pp; sp.D = f->D; sp.W = f->W; sp.V = f->V;
+  sp.cnt = f->cnt; sp.prev_xy = f->prev_xy; sp.status = f->status;
+  sp.pose = nullptr; sp.xy = f->pend_xy; sp.ids = f->pend_ids; sp.action = nullptr;
+  sp.m = mc; sp.do_predict = 0; sp.finish = f->pend_finish;
+  sp.assoc_out = assoc_dev;
+  sp.pose_out = pose_out_dev ? pose_out_dev : reinterpret_cast<double *>(f->res_dev + res.pose);
+  sp.cnt_out = count_dev ? count_dev : reinterpret_cast<int *>(f->res_dev + res.cnt);
+  sp.side_mode = 1; sp.cols = f->cols; sp.guess = f->guess;
+  sp.done_out = done_dev ? done_dev : f->done_dev;
+  sp.bar = f->bar; sp.bar_base = f->bar_base;
+  sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
+  f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
+  f->pend_m = -1;
+
+  const bool timed = f->ev_cap > 0;
+  const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 3 : 0;
+  if (timed) CK(f, cudaEventRecord(f->ev[slot], f->stream));
+  void *args[] = {(void *)&sp};
+  CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel, dim3(f->seq_grid), dim3(kSeqThreads), args, 0,
+                                    f->stream));
+  f->launches++;
+  if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
+  DdParams dp{};
+  dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
+  dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;
+  dp.lay = f->lay; dp.row_begin = f->lay.rb; dp.row_end = f->lay.re;
+  dp.prefetch_ahead = f->dd_prefetch;
+  dp.total_chunks = dd_total_chunks(32, dp.row_begin, dp.row_end);
+  long long grid = (long long)f->dd_grid * f->dd_ctas;
+  if (grid > dp.total_chunks) grid = dp.total_chunks;
+  ekf_downdate_kernel<32, false><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
+  shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
+  f->launches += 2;
+  CK(f, cudaGetLastError());
+  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); f->ev_count++; }
+  return EKF_OK;
+}
+
+}  // extern "C"

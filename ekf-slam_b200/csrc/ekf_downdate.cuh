@@ -45,6 +45,7 @@ struct DdParams {
   double *sigma;
   const double *V;   // row operand  (K panels)
   const double *W;   // column operand (G panels)
+  EkfLay lay;                // rows stored by this handle (whole matrix or one row shard)
   int n_pad, kmax, k2;       // k2 = panel columns in use, a multiple of 4
   int row_begin, row_end;    // rows handled by this launch (multiples of 64); whole matrix: 0, n_pad
   long long total_chunks;
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kerne
         if (it >= kDdVStages) mbar_wait(&done[s], ((it / kDdVStages) - 1) & 1);
         for (; p.prefetch_ahead > 0 && pf_it <= it + p.prefetch_ahead && pf_it < n_chunks; ++pf_it) {
           if (pf_it >= 2) {      // chunks 0 and 1 are fetched by the compute warps right away
-            const double *src = p.sigma + ekf_elem(p.n_pad, pf.row, pf.J * EKF_STRIP);
+            const double *src = p.sigma + ekf_lay_elem(p.lay, pf.row, pf.J * EKF_STRIP);
             bulk_prefetch_l2(src, kChunkBytes);
           }
           dd_advance(pf, CR, p.row_begin, p.row_end);
@@ -229,7 +230,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kerne
   ChunkCursor cur = dd_seek(c_begin, CR, p.row_begin, p.row_end);
   double c[4][4][2], cn[PF ? 4 : 1][4][2];
   if (PF) {
-    const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+    const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -241,12 +242,12 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kerne
   const int ksteps = k2 >> 2;
   for (int it = 0; it < n_chunks; ++it) {
     const int s = it % kDdVStages;
-    double *out = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+    double *out = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
     const int curJ = cur.J;
     dd_advance(cur, CR, p.row_begin, p.row_end);
     if (PF) {
       if (it + 1 < n_chunks) {       // prefetch the next chunk's tile into the second register set
-        const double *base = p.sigma + ekf_elem(p.n_pad, cur.row, cur.J * EKF_STRIP);
+        const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll

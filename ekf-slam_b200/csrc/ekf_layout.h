@@ -50,6 +50,43 @@ EKF_HD int64_t ekf_elem(int n_pad, int i, int j) {
 EKF_HD int64_t ekf_elem_sym(int n_pad, int i, int j) {
   return i >= j ? ekf_elem(n_pad, i, j) : ekf_elem(n_pad, j, i);
 }
+
+/* ---- row-sharded storage (one large map over several GPUs) --------------------------------------
+ * A shard owns the rows [rb, re) of the lower triangle (rb, re multiples of 128, re <= n_pad) and stores
+ * them in the same column strips: strip J holds columns [128J, 128J+128) for rows [max(128J, rb), re).
+ * rb = 0, re = n_pad is the whole matrix and gives exactly the offsets of the functions above. */
+typedef struct EkfLay { int rb, re; } EkfLay;
+EKF_HD EkfLay ekf_lay_full(int n_pad) { EkfLay l; l.rb = 0; l.re = n_pad; return l; }
+EKF_HD int ekf_lay_first_row(EkfLay l, int J) { return J * EKF_STRIP > l.rb ? J * EKF_STRIP : l.rb; }
+EKF_HD int64_t ekf_lay_strip_offset(EkfLay l, int J) {
+  const int Jb = l.rb / EKF_STRIP;
+  if (J <= Jb) return (int64_t)EKF_STRIP * J * (l.re - l.rb);
+  const int64_t head = (int64_t)EKF_STRIP * Jb * (l.re - l.rb);
+  const int64_t cnt = J - Jb;
+  const int64_t tri = (int64_t)J * (J - 1) / 2 - (int64_t)Jb * (Jb - 1) / 2;
+  return head + (int64_t)EKF_STRIP * (cnt * l.re - (int64_t)EKF_STRIP * tri);
+}
+EKF_HD int64_t ekf_lay_elems(EkfLay l) { return ekf_lay_strip_offset(l, l.re / EKF_STRIP); }
+/* requires rb <= i < re and i >= (j & ~127) */
+EKF_HD int64_t ekf_lay_elem(EkfLay l, int i, int j) {
+  const int J = j / EKF_STRIP;
+  return ekf_lay_strip_offset(l, J) + (int64_t)(i - ekf_lay_first_row(l, J)) * EKF_STRIP + (j - J * EKF_STRIP);
+}
+EKF_HD int ekf_lay_owns_row(EkfLay l, int i) { return i >= l.rb && i < l.re; }
+/* equal-area split of the triangle over `count` shards: boundary g at n_pad * sqrt(g / count), rounded
+ * to the strip width; shard g owns [bound(g), bound(g+1)) */
+EKF_HD int ekf_shard_bound(int n_pad, int g, int count) {
+  if (g <= 0) return 0;
+  if (g >= count) return n_pad;
+  /* integer square root of n_pad^2 * g / count */
+  const int64_t x = (int64_t)n_pad * n_pad * g / count;
+  int64_t r = n_pad;
+  while (r * r > x) r = (r + x / r) / 2;
+  int b = (int)((r + EKF_STRIP / 2) / EKF_STRIP) * EKF_STRIP;
+  if (b > n_pad) b = n_pad;
+  return b;
+}
+
 /* W / V panels: n_pad rows x kmax columns (kmax a multiple of 4), laid out for the fp64 tensor-core
  * fragments of the covariance pass (mma.m8n8k4): [row / 32][k / 4][slot(row % 32)][k % 4].
  *   - a 32-row block of the first k2 columns is one contiguous range of k2 * 256 bytes (one bulk copy);

@@ -73,6 +73,15 @@ struct SeqParams {
   int *assoc_out;         // device m or nullptr
   double *pose_out;       // device 3 (always written)
   int *cnt_out;           // device 1 (always written)
+  // storage geometry of this handle's rows (whole matrix, or one row shard)
+  EkfLay lay;
+  // row-sharded handles (ekf_shard.cuh): side_mode = 1 means Pp / D are persistent and current (Sigma
+  // is not read at all here), `cols` holds the all-reduced raw Sigma_0 columns of the guessed
+  // landmarks, [slot][row][2]; guess[s] = landmark whose columns slot s holds (-1 = none)
+  int side_mode;
+  const double *cols;
+  const int *guess;
+  int *done_out;          // measurements actually processed (a failed speculation stops the scan early)
   // grid barrier + arg-min slots
   unsigned long long *bar;
   unsigned long long bar_base;
@@ -113,6 +122,7 @@ __device__ __forceinline__ double4 ldcg_d4(const double4 *p) {
 struct Bcast {
   int j;        // associated landmark, or -1 when the measurement is skipped
   int is_new;   // the landmark's state is (re)initialised from the sighting
+  int slot;     // sharded: column slot of landmark j (-1: fresh landmark, columns are zero; -2: missing)
   double lx, ly;             // landmark j position used when is_new
   double rec[kRecStride];    // update record (layout above)
 };
@@ -132,6 +142,7 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   __shared__ double s_wa[kMaxK2], s_wb[kMaxK2];
   __shared__ int s_cnt;
   __shared__ double s_pred[2];    // (-dy, dx)
+  __shared__ double s_pb0[3][3];  // pose block right after the prediction (what Sigma_0 holds)
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -148,7 +159,9 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
 #pragma unroll
     for (int i = 0; i < 3; ++i)
 #pragma unroll
-      for (int j = 0; j <= i; ++j) P[i][j] = P[j][i] = strip0[i * EKF_STRIP + j];
+      for (int j = 0; j <= i; ++j)
+        P[i][j] = P[j][i] = p.side_mode ? (j == 0 ? p.Pp[i].x : j == 1 ? p.Pp[i].y : p.Pp[i].z)
+                                        : strip0[i * EKF_STRIP + j];
     if (p.do_predict) {
       const double th = normalize_angle(p.pose[0]);          // slam.cpp:186
       const double x = p.pose[1], y = p.pose[2];             // slam.cpp:187-188
@@ -179,18 +192,15 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
     for (int i = 0; i < 3; ++i)
 #pragma unroll
       for (int j = 0; j <= i; ++j) s_pb[i][j] = s_pb[j][i] = P[i][j];  // lower triangle rules
-    if (blockIdx.x == 0) {
 #pragma unroll
-      for (int i = 0; i < 3; ++i) {
+    for (int i = 0; i < 3; ++i)
 #pragma unroll
-        for (int j = 0; j <= i; ++j) strip0[i * EKF_STRIP + j] = P[i][j];
-        p.Pp[i] = make_double4(s_pb[i][0], s_pb[i][1], s_pb[i][2], 0.0);
-        p.mu[i] = s_ps[i];
-      }
-    }
+      for (int j = 0; j < 3; ++j) s_pb0[i][j] = s_pb[i][j];
+    // the pose block / pose state in global memory are rewritten in the epilogue, AFTER a grid
+    // barrier: every CTA reads the old values above, in no particular order
   }
   __syncthreads();
-  {
+  if (!p.side_mode) {
     const double ndy = s_pred[0], pdx = s_pred[1];
     for (int k = gtid; k < p.N; k += nthreads_total) {
       const int a = 4 + 2 * k;
@@ -204,7 +214,7 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
         *ra = va; *rb = vb;
       }
       p.Pp[a] = va; p.Pp[a + 1] = vb;
-      const double *dg = p.sigma + ekf_elem(n_pad, a, a);
+      const double *dg = p.sigma + ekf_lay_elem(p.lay, a, a);
       const double2 d0 = *reinterpret_cast<const double2 *>(dg);                // (a,a), (a,b) scratch
       const double2 d1 = *reinterpret_cast<const double2 *>(dg + EKF_STRIP);    // (b,a), (b,b)
       p.D[k] = make_double4(d0.x, d1.x, d1.y, 0.0);
@@ -214,6 +224,7 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   // ---------------- measurement loop --------------------------------------------------------
   const bool unknown = (p.ids == nullptr);
   const int G = (int)gridDim.x;
+  int done = p.m;
   for (int t = 0; t < p.m; ++t) {
     const double mx = p.xy[2 * t], my = p.xy[2 * t + 1];
     const Polar z = to_polar(mx, my);                        // slam.cpp:345-347
@@ -398,6 +409,23 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
     }
     __syncthreads();
     const int j = s_b.j;
+    // sharded handle: which slot of the exchanged column buffer holds landmark j's raw Sigma_0 columns
+    int slot = -1;
+    if (p.cols != nullptr && j >= 0 && !(unknown && s_b.is_new)) {
+      slot = -2;
+      if (__ldg(p.guess + t) == j) slot = t;
+      else
+        for (int s2 = 0; s2 < p.m; ++s2)
+          if (__ldg(p.guess + s2) == j) { slot = s2; break; }
+    }
+    if (slot == -2) {
+      // failed speculation (identical decision in every thread of the grid): stop before measurement
+      // t is applied; the host runs another round for the rest.  Pay the barrier arrivals the host
+      // has already accounted for.
+      if (tid == 0 && p.m - t - 1 > 0) atomicAdd(p.bar, (unsigned long long)(p.m - t - 1));
+      done = t;
+      break;
+    }
 
     // ---- pose rows: gain, state and pose-block update (slam.cpp:476,482,485-486 restricted to
     //      rows/cols 0..2), redundantly in every CTA, one lane per pose row ------------------------
@@ -457,13 +485,22 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
         if (k == j) {
           q00 = s_b.rec[19]; q01 = s_b.rec[20]; q10 = s_b.rec[20]; q11 = s_b.rec[21];
         } else {
-          if (k > j) {
-            const double *src = p.sigma + ekf_elem(n_pad, a, aj);
+          if (p.cols != nullptr) {
+            if (slot >= 0) {             // exchanged raw columns, [slot][row][2]
+              const double *src = p.cols + ((int64_t)slot * n_pad + a) * 2;
+              const double2 r0 = __ldcg(reinterpret_cast<const double2 *>(src));
+              const double2 r1 = __ldcg(reinterpret_cast<const double2 *>(src + 2));
+              q00 = r0.x; q01 = r0.y; q10 = r1.x; q11 = r1.y;
+            } else {                     // landmark created in this scan: Sigma_0 column is zero
+              q00 = 0.0; q01 = 0.0; q10 = 0.0; q11 = 0.0;
+            }
+          } else if (k > j) {
+            const double *src = p.sigma + ekf_lay_elem(p.lay, a, aj);
             const double2 r0 = __ldg(reinterpret_cast<const double2 *>(src));
             const double2 r1 = __ldg(reinterpret_cast<const double2 *>(src + EKF_STRIP));
             q00 = r0.x; q01 = r0.y; q10 = r1.x; q11 = r1.y;
           } else {
-            const double *src = p.sigma + ekf_elem(n_pad, aj, a);
+            const double *src = p.sigma + ekf_lay_elem(p.lay, aj, a);
             const double2 c0 = __ldg(reinterpret_cast<const double2 *>(src));
             const double2 c1 = __ldg(reinterpret_cast<const double2 *>(src + EKF_STRIP));
             q00 = c0.x; q10 = c0.y; q01 = c1.x; q11 = c1.y;
@@ -526,10 +563,9 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
     __syncthreads();  // s_b / s_wa / s_ps are rewritten by the next measurement
   }
 
-  // pad columns [2m, round-up-to-4(2m)) of both panels are zeroed: the covariance pass works on
-  // whole k-steps of 4 columns
-  if ((2 * p.m) & 2) {
-    const int qz = 2 * p.m;
+  // columns [2 * done, round-up-to-4(2m)) of both panels are zeroed: the covariance pass works on whole
+  // k-steps of 4 columns (and, after a stopped scan, on the columns the host sized it for)
+  for (int qz = 2 * done; qz < ((2 * p.m + 3) & ~3); qz += 2) {
     const double2 zero = make_double2(0.0, 0.0);
     for (int k = gtid; k < p.N; k += nthreads_total) {
       const int a = 4 + 2 * k;
@@ -545,12 +581,26 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   }
 
   // ---------------- epilogue: slam.cpp:273-274,291 / :490-491,508 ---------------------------------
+  // a scan without measurements has passed no grid barrier yet: the global pose block / pose state
+  // below may only be rewritten once every CTA has read the old ones
+  if (p.m == 0) grid_barrier(p.bar, p.bar_base + gridDim.x);
   if (blockIdx.x == 0 && tid == 0) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      if (p.side_mode) {
+        p.Pp[i] = make_double4(s_pb[i][0], s_pb[i][1], s_pb[i][2], 0.0);     // current block, persistent
+      } else {
+        p.Pp[i] = make_double4(s_pb0[i][0], s_pb0[i][1], s_pb0[i][2], 0.0);
+#pragma unroll
+        for (int j = 0; j <= i; ++j) strip0[i * EKF_STRIP + j] = s_pb0[i][j];  // Sigma_0 after prediction
+      }
+    }
     p.mu[0] = s_ps[0]; p.mu[1] = s_ps[1]; p.mu[2] = s_ps[2];
     *p.cnt = s_cnt;
     *p.cnt_out = s_cnt;
     p.pose_out[0] = s_ps[0]; p.pose_out[1] = s_ps[1]; p.pose_out[2] = s_ps[2];
-    if (p.finish) { p.prev_xy[0] = s_ps[1]; p.prev_xy[1] = s_ps[2]; }
+    if (p.finish && done == p.m) { p.prev_xy[0] = s_ps[1]; p.prev_xy[1] = s_ps[2]; }
+    if (p.done_out) *p.done_out = done;
   }
 }
 

@@ -1,0 +1,211 @@
+// Row-sharded single large map (BASELINE configs 4-5 on 2/4/8 GPUs): the small kernels around the
+// exchange step.  One process per GPU; shard g owns the rows [rb, re) of Sigma's lower triangle
+// (equal-area split, ekf_layout.h).  Everything O(n) is REPLICATED and computed redundantly and
+// identically on every rank: state, pose panel Pp, diagonal blocks D, the W / V panels, the
+// association decisions.  Per scan there is ONE exchange:
+//
+//   begin   (this file)  prediction on the replicated pose panel (slam.cpp:186-198 / :323-335);
+//                        speculative association of all m sightings against the scan-start state
+//                        -> guess[t]; every rank writes the part it owns of the raw Sigma_0 columns
+//                        of the guessed landmarks into the exchange buffer (zeros elsewhere)
+//   caller               sum-all-reduce of the buffer (NCCL over NVLink / NVSwitch; m * n_pad * 2
+//                        doubles = 6.4 MB at N = 10,000, m = 20).  Each element has exactly one
+//                        non-zero contributor, so the sum is exact.
+//   finish  (ekf_seq.cuh + ekf_downdate.cuh)  the unchanged sequential phase, replicated, reading
+//                        the columns from the buffer instead of Sigma; it re-derives every association
+//                        with the reference's sequential semantics and STOPS if a decision ever needs
+//                        a landmark that was not guessed (the caller then runs another round for the
+//                        rest of the scan).  Then each rank applies the rank-2m downdate to its own rows
+//                        and writes Pp / D back into the Sigma entries they mirror.
+//
+// Pp and D are persistent between scans on a sharded handle (no per-scan extraction); after a
+// fixture call (fill / set) they are rebuilt once by side_extract + one more all-reduce.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ekf_layout.h"
+#include "ekf_math.cuh"
+
+namespace ekf {
+
+// ---- prediction on the replicated side state ------------------------------------------------------
+__global__ void shard_predict_kernel(double4 *Pp, double *mu, const double *pose, const double *prev_xy, int N,
+                                     double q_noise) {
+  const double th = normalize_angle(pose[0]);              // slam.cpp:186
+  const double x = pose[1], y = pose[2];
+  const double dx = x - prev_xy[0], dy = y - prev_xy[1];   // slam.cpp:190-191
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int k = gtid; k < N; k += gridDim.x * blockDim.x) {
+    const int a = 4 + 2 * k;
+    double4 va = Pp[a], vb = Pp[a + 1];
+    va.y = va.x * (-dy) + va.y; va.z = va.x * dx + va.z;
+    vb.y = vb.x * (-dy) + vb.y; vb.z = vb.x * dx + vb.z;
+    Pp[a] = va; Pp[a + 1] = vb;
+  }
+  if (gtid == 0) {
+    double P[3][3], Bm[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double4 r = Pp[i];
+      P[i][0] = r.x; P[i][1] = r.y; P[i][2] = r.z;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < i; ++j) P[j][i] = P[i][j];        // lower triangle rules
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      Bm[0][j] = P[0][j];
+      Bm[1][j] = (-dy) * P[0][j] + P[1][j];
+      Bm[2][j] = dx * P[0][j] + P[2][j];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      P[i][0] = Bm[i][0];
+      P[i][1] = Bm[i][0] * (-dy) + Bm[i][1];
+      P[i][2] = Bm[i][0] * dx + Bm[i][2];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) P[i][i] += q_noise;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < i; ++j) P[j][i] = P[i][j];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) Pp[i] = make_double4(P[i][0], P[i][1], P[i][2], 0.0);
+    mu[0] = th; mu[1] = x; mu[2] = y;
+  }
+}
+
+// ---- speculative association: one CTA per sighting, against the scan-start state ------------------
+constexpr int kGuessThreads = 256;
+__global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double4 *Pp, const double4 *D,
+                                                                   const double *mu, const int *cnt_p,
+                                                                   const double *xy, const int *ids, int *guess,
+                                                                   double r_noise, double thr) {
+  __shared__ Cand s_red[kGuessThreads / 32];
+  const int t = blockIdx.x;
+  if (ids != nullptr) {                                    // known association: nothing to speculate
+    if (threadIdx.x == 0) guess[t] = ids[t];
+    return;
+  }
+  const int cnt = *cnt_p;
+  const Polar z = to_polar(xy[2 * t], xy[2 * t + 1]);
+  const double th = mu[0], px = mu[1], py = mu[2];
+  double pb[3][3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double4 r = Pp[i];
+    pb[i][0] = r.x; pb[i][1] = r.y; pb[i][2] = r.z;
+  }
+  Cand best{INFINITY, 0x7fffffff};
+  for (int k = threadIdx.x; k < cnt; k += kGuessThreads) {
+    const int a = 4 + 2 * k;
+    const double2 lm = *reinterpret_cast<const double2 *>(mu + a);
+    const double4 pa = Pp[a], pbr = Pp[a + 1], dk = D[k];
+    const Lin L = linearize(th, px, py, lm.x, lm.y);
+    const double par3[3] = {pa.x, pa.y, pa.z}, pbr3[3] = {pbr.x, pbr.y, pbr.z};
+    const Block5 B = make_block5(pb, par3, pbr3, dk.x, dk.y, dk.z);
+    const Innov I = innovation(B, L, r_noise);
+    const double zd0 = z.r - L.zhat_r, zd1 = normalize_angle(z.phi - L.zhat_b);
+    double i00, i01, i11;
+    const double d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
+    best = cand_min(best, Cand{d, k});
+  }
+  best = warp_argmin(best);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    Cand c = s_red[0];
+    for (int w = 1; w < kGuessThreads / 32; ++w) c = cand_min(c, s_red[w]);
+    // generous acceptance (4 x threshold): a sighting that is borderline now may match after the
+    // earlier updates of the scan; an unnecessary column costs nothing but bandwidth
+    guess[t] = (c.k < cnt && c.d <= 4.0 * thr) ? c.k : -1;
+  }
+}
+
+// ---- exchange buffer: this rank's part of the raw Sigma_0 columns of the guessed landmarks --------
+// cols[slot][row][2] = (Sigma_0[row, a_j], Sigma_0[row, b_j]) for row outside the landmark's own 2x2
+// block; every element is written by every rank (zero unless owned).
+__global__ void shard_extract_cols_kernel(const double *sigma, EkfLay lay, int n_pad, int N, const int *guess,
+                                          int m, double *cols) {
+  const int64_t total = (int64_t)m * n_pad;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int slot = (int)(e / n_pad), i = (int)(e % n_pad);
+    const int j = guess[slot];
+    double2 v = make_double2(0.0, 0.0);
+    if (j >= 0 && j < N) {
+      const int a = 4 + 2 * j;
+      if (i > a + 1) {
+        if (ekf_lay_owns_row(lay, i)) v = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a));
+      } else if (i < a) {
+        if (ekf_lay_owns_row(lay, a)) {
+          v.x = sigma[ekf_lay_elem(lay, a, i)];
+          v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
+        }
+      }
+    }
+    *reinterpret_cast<double2 *>(cols + e * 2) = v;
+  }
+}
+
+// ---- side state <-> Sigma -----------------------------------------------------------------------
+// side[0 .. 4 n_pad) = Pp rows (x, y, z, 0), side[4 n_pad ..) = D blocks (aa, ba, bb, 0): this rank's
+// owned rows, zero elsewhere (summed over the ranks afterwards)
+__global__ void shard_side_extract_kernel(const double *sigma, EkfLay lay, int n_pad, int N, double4 *Pp, double4 *D) {
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int i = gtid; i < n_pad; i += gridDim.x * blockDim.x) {
+    double4 v = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (ekf_lay_owns_row(lay, i) && i != 3) {
+      const double *r = sigma + ekf_lay_elem(lay, i, 0);
+      v.x = r[0];
+      if (i >= 1) v.y = r[1];
+      if (i >= 2) v.z = r[2];
+      if (i < 3) {                                         // pose block: mirror the stored lower part
+        if (i == 0) { v.y = 0.0; v.z = 0.0; }
+        if (i == 1) v.z = 0.0;
+      }
+    }
+    Pp[i] = v;
+  }
+  for (int k = gtid; k < N; k += gridDim.x * blockDim.x) {
+    const int a = 4 + 2 * k;
+    double4 v = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (ekf_lay_owns_row(lay, a)) {
+      const double *dg = sigma + ekf_lay_elem(lay, a, a);
+      v.x = dg[0]; v.y = dg[EKF_STRIP]; v.z = dg[EKF_STRIP + 1];
+    }
+    D[k] = v;
+  }
+}
+// after the all-reduce the pose block rows hold only their lower part: make it fully symmetric
+__global__ void shard_side_fix_pose_kernel(double4 *Pp) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    double4 r0 = Pp[0], r1 = Pp[1], r2 = Pp[2];
+    r0.y = r1.x; r0.z = r2.x; r1.z = r2.y;
+    Pp[0] = r0; Pp[1] = r1;
+  }
+}
+// Pp / D -> the Sigma entries they mirror (owned rows only); run after the covariance pass
+__global__ void shard_side_writeback_kernel(double *sigma, EkfLay lay, int n_pad, int N, const double4 *Pp,
+                                            const double4 *D) {
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int i = gtid; i < n_pad; i += gridDim.x * blockDim.x) {
+    if (!ekf_lay_owns_row(lay, i) || i == 3) continue;
+    const double4 v = Pp[i];
+    double *r = sigma + ekf_lay_elem(lay, i, 0);
+    r[0] = v.x;
+    if (i >= 1) r[1] = v.y;
+    if (i >= 2) r[2] = v.z;
+  }
+  for (int k = gtid; k < N; k += gridDim.x * blockDim.x) {
+    const int a = 4 + 2 * k;
+    if (!ekf_lay_owns_row(lay, a)) continue;
+    const double4 v = D[k];
+    double *dg = sigma + ekf_lay_elem(lay, a, a);
+    dg[0] = v.x; dg[EKF_STRIP] = v.y; dg[EKF_STRIP + 1] = v.z;
+  }
+}
+
+}  // namespace ekf

@@ -10,28 +10,32 @@
 namespace ekf {
 
 // Sigma_0 = diag(0, 0, 0, prior * I_2N): slam.cpp:128-132 (storage was zero-filled before).
-__global__ void init_prior_kernel(double *sigma, int n_pad, int n_int, double prior) {
+__global__ void init_prior_kernel(double *sigma, EkfLay lay, int n_int, double prior) {
   const int i = 4 + blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n_int) sigma[ekf_elem(n_pad, i, i)] = prior;
+  if (i < n_int && ekf_lay_owns_row(lay, i)) sigma[ekf_lay_elem(lay, i, i)] = prior;
 }
 
-// out[(i-i0)*ld + (j-j0)] = Sigma[i][j] (external indices, symmetric fill)
-__global__ void get_block_kernel(const double *sigma, int n_pad, int i0, int i1, int j0, int j1, double *out) {
+// out[(i-i0)*ld + (j-j0)] = Sigma[i][j] (external indices, symmetric fill); entries whose stored
+// element belongs to another row shard read as 0 (the caller sums over the shards)
+__global__ void get_block_kernel(const double *sigma, EkfLay lay, int i0, int i1, int j0, int j1, double *out) {
   const int64_t ld = j1 - j0;
   const int64_t total = (int64_t)(i1 - i0) * ld;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     const int i = i0 + (int)(e / ld), j = j0 + (int)(e % ld);
-    out[e] = sigma[ekf_elem_sym(n_pad, ekf_int_index(i), ekf_int_index(j))];
+    const int ii = ekf_int_index(i), jj = ekf_int_index(j);
+    const int r = ii >= jj ? ii : jj, c = ii >= jj ? jj : ii;
+    out[e] = ekf_lay_owns_row(lay, r) ? sigma[ekf_lay_elem(lay, r, c)] : 0.0;
   }
 }
 
 // writes the entries of the block with row >= col into the stored triangle
-__global__ void set_block_kernel(double *sigma, int n_pad, int i0, int i1, int j0, int j1, const double *in) {
+__global__ void set_block_kernel(double *sigma, EkfLay lay, int i0, int i1, int j0, int j1, const double *in) {
   const int64_t ld = j1 - j0;
   const int64_t total = (int64_t)(i1 - i0) * ld;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     const int i = i0 + (int)(e / ld), j = j0 + (int)(e % ld);
-    if (i >= j) sigma[ekf_elem(n_pad, ekf_int_index(i), ekf_int_index(j))] = in[e];
+    if (i >= j && ekf_lay_owns_row(lay, ekf_int_index(i)))
+      sigma[ekf_lay_elem(lay, ekf_int_index(i), ekf_int_index(j))] = in[e];
   }
 }
 
@@ -62,18 +66,19 @@ __device__ inline double proc_u(uint64_t seed, int i, int r) { return 0.01 * has
 
 // Sigma = Dblk + U U^T on the `count` mapped landmarks and the pose; unmapped landmarks keep the
 // reference prior on their diagonal and zero elsewhere.  One thread per stored entry.
-__global__ void fill_procedural_sigma_kernel(double *sigma, int n_pad, int count, uint64_t seed, double prior) {
-  const int64_t total = ekf_sigma_elems(n_pad);
+__global__ void fill_procedural_sigma_kernel(double *sigma, EkfLay lay, int n_pad, int count, uint64_t seed,
+                                             double prior) {
+  const int64_t total = ekf_lay_elems(lay);
   const int n_active = 4 + 2 * count;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     // invert the strip layout: find strip J with strip_offset(J) <= e
-    int lo = 0, hi = n_pad / EKF_STRIP - 1;
+    int lo = 0, hi = lay.re / EKF_STRIP - 1;
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
-      if (ekf_strip_offset(n_pad, mid) <= e) lo = mid; else hi = mid - 1;
+      if (ekf_lay_strip_offset(lay, mid) <= e) lo = mid; else hi = mid - 1;
     }
-    const int64_t rel = e - ekf_strip_offset(n_pad, lo);
-    const int i = lo * EKF_STRIP + (int)(rel / EKF_STRIP), j = lo * EKF_STRIP + (int)(rel % EKF_STRIP);
+    const int64_t rel = e - ekf_lay_strip_offset(lay, lo);
+    const int i = ekf_lay_first_row(lay, lo) + (int)(rel / EKF_STRIP), j = lo * EKF_STRIP + (int)(rel % EKF_STRIP);
     double v = 0.0;
     const int n_int_all = n_pad;  // rows beyond the real dimension stay zero through the test below
     (void)n_int_all;

@@ -1,0 +1,180 @@
+"""Host-side drivers of the row-sharded large map (include/ekf_slam_b200.h, ekf_shard_*).
+
+The C ABI leaves the one exchange per scan round to the caller.  Two callers live here:
+
+  * `ShardedEkf`   one rank of a torch.distributed job (one process per GPU): the exchange is
+                   `dist.all_reduce(SUM)` over NCCL on a tensor that aliases the handle's buffer;
+  * `LocalShards`  R handles on ONE GPU (how the multi-rank path is exercised on a single-GPU test
+                   box): the exchange is a plain sum of the R buffers.
+
+torch is used for device buffers, streams and the collective only.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import EkfSlam
+
+MAX_ROUND = 24   # kMaxChunkM: sightings per round
+
+
+class _DevBuf:
+    """zero-copy view of a raw device buffer of doubles for torch.as_tensor"""
+
+    def __init__(self, ptr: int, count: int):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+def alias(ptr: int, count: int, device) -> torch.Tensor:
+    return torch.as_tensor(_DevBuf(ptr, count), device=device)
+
+
+def shard_bounds(n_landmarks: int, count: int):
+    """row boundaries of the equal-area split (mirrors ekf_shard_bound in csrc/ekf_layout.h)"""
+    n_pad = (4 + 2 * n_landmarks + 127) // 128 * 128
+    out = []
+    for g in range(count + 1):
+        if g == 0:
+            out.append(0)
+        elif g == count:
+            out.append(n_pad)
+        else:
+            x = n_pad * n_pad * g // count
+            r = int(np.floor(np.sqrt(float(x))))
+            while r * r > x:
+                r -= 1
+            while (r + 1) * (r + 1) <= x:
+                r += 1
+            out.append(min((r + 64) // 128 * 128, n_pad))
+    return out
+
+
+class _Driver:
+    """round loop shared by both callers; subclasses provide handles() and exchange(list of (ptr, count))"""
+
+    def _setup(self, device):
+        self.device = device
+        self._done = torch.zeros(1, dtype=torch.int32, device=device)
+        self._cnt = torch.zeros(1, dtype=torch.int32, device=device)
+        self._pose_out = torch.zeros(3, dtype=torch.float64, device=device)
+
+    def sync(self):
+        bufs = [h.shard_sync_begin() for h in self.handles()]
+        self.exchange(bufs)
+        for h in self.handles():
+            h.shard_sync_finish()
+
+    def scan_dev(self, pose_t, xy_t, assoc_t, ids_t=None, check: bool = True):
+        """One scan from device tensors: pose_t [3], xy_t [m, 2], assoc_t int32 [m] (written).
+        With check=False a single round is enqueued without reading `done` back (fully asynchronous;
+        valid when m <= 24 and the speculation holds - inspect self._done afterwards)."""
+        m = xy_t.shape[0]
+        t0, first, rounds = 0, True, 0
+        while t0 < m:
+            rem = m - t0
+            last = rem <= MAX_ROUND
+            bufs = [h.shard_scan_begin(pose_t.data_ptr() if first else 0, rem, xy_t[t0:].data_ptr(),
+                                       ids_t[t0:].data_ptr() if ids_t is not None else 0, last)
+                    for h in self.handles()]
+            self.exchange(bufs)
+            for h in self.handles():
+                h.shard_scan_finish(assoc_t[t0:].data_ptr(), self._done.data_ptr(), self._pose_out.data_ptr(),
+                                    self._cnt.data_ptr())
+            rounds += 1
+            first = False
+            if not check:
+                return rounds
+            done = int(self._done.item())
+            if done == 0 and rounds > 4 * m + 4:
+                raise RuntimeError("sharded scan makes no progress")
+            t0 += done
+        return rounds
+
+    def scan(self, pose, xy, ids=None):
+        """host arrays in, (assoc, count, pose_after, rounds) out"""
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
+        pose_t = torch.from_numpy(np.ascontiguousarray(pose, dtype=np.float64)).to(self.device)
+        xy_t = torch.from_numpy(xy).to(self.device)
+        ids_t = None if ids is None else torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int32)).to(self.device)
+        assoc_t = torch.full((len(xy),), -7, dtype=torch.int32, device=self.device)
+        rounds = self.scan_dev(pose_t, xy_t, assoc_t, ids_t)
+        return assoc_t.cpu().numpy(), int(self._cnt.item()), self._pose_out.cpu().numpy(), rounds
+
+
+class LocalShards(_Driver):
+    """R row shards of one map as R handles on one GPU (test / single-GPU emulation of R ranks)."""
+
+    def __init__(self, n_landmarks: int, shards: int, device_index: int = 0, **kw):
+        self.hs = [EkfSlam(n_landmarks=n_landmarks, device=device_index, shard_rank=r, shard_count=shards, **kw)
+                   for r in range(shards)]
+        self._setup(torch.device("cuda", device_index))
+        self.n = self.hs[0].n
+        stream = torch.cuda.current_stream(self.device)
+        if stream.cuda_stream != 0:
+            for h in self.hs:
+                h.set_stream(stream.cuda_stream)
+        self._own_stream = stream.cuda_stream == 0
+
+    def handles(self):
+        return self.hs
+
+    def exchange(self, bufs):
+        if self._own_stream:            # handles run on their own streams: order by synchronising
+            for h in self.hs:
+                h.synchronize()
+        ts = [alias(p, c, self.device) for (p, c) in bufs]
+        total = ts[0].clone()
+        for t in ts[1:]:
+            total += t
+        for t in ts:
+            t.copy_(total)
+        if self._own_stream:
+            torch.cuda.synchronize(self.device)
+
+    # fixtures applied to every shard
+    def fill_procedural(self, seed, count, grid_w):
+        for h in self.hs:
+            h.fill_procedural(seed, count, grid_w)
+
+    def set_previous_xy(self, x, y):
+        for h in self.hs:
+            h.set_previous_xy(x, y)
+
+    def state(self):
+        return self.hs[0].state()
+
+    def sigma_block(self, i0, i1, j0, j1):
+        return sum(h.sigma_block(i0, i1, j0, j1) for h in self.hs)
+
+    def sigma(self):
+        return self.sigma_block(0, self.n, 0, self.n)
+
+    def close(self):
+        for h in self.hs:
+            h.close()
+
+
+class ShardedEkf(_Driver):
+    """This process' row shard of one map in a torch.distributed job (NCCL all-reduce per round)."""
+
+    def __init__(self, n_landmarks: int, rank: int, world: int, device_index: int, stream=None, group=None, **kw):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.h = EkfSlam(n_landmarks=n_landmarks, device=device_index, shard_rank=rank, shard_count=world, **kw)
+        self._setup(torch.device("cuda", device_index))
+        self.n = self.h.n
+        stream = stream or torch.cuda.current_stream(self.device)
+        if stream.cuda_stream == 0:
+            raise ValueError("ShardedEkf needs a non-default torch stream (ekf_set_stream reads 0 as 'own stream')")
+        self.h.set_stream(stream.cuda_stream)
+
+    def handles(self):
+        return [self.h]
+
+    def exchange(self, bufs):
+        (p, c), = bufs
+        self.dist.all_reduce(alias(p, c, self.device), op=self.dist.ReduceOp.SUM, group=self.group)
+
+    def close(self):
+        self.h.close()

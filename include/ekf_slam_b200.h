@@ -143,6 +143,35 @@ int ekf_launch_count(ekf_filter *f, int64_t *launches);
 int ekf_enable_timing(ekf_filter *f, int32_t ring_scans);
 int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t max_scans, int32_t *n_scans);
 
+/* ---- one large map row-sharded over several GPUs (BASELINE configs 4-5 at 2/4/8 GPUs) ------------
+ * One process (or one handle) per GPU, created with cfg.shard_rank / cfg.shard_count: the handle
+ * stores the rows [row_begin, row_end) of Sigma's lower triangle (equal-area split) and a REPLICA of
+ * everything O(n) (state, pose panel, diagonal blocks, counters).  Every call below must be made on
+ * every rank with identical arguments.  The library does not talk to the other ranks: each phase
+ * hands back a device buffer that the caller SUM-all-reduces over the ranks (NCCL `ncclAllReduce`,
+ * ncclDouble / ncclSum, on the handle's stream) before the matching finish call.
+ *   ekf_shard_sync_*   rebuilds the replicated side state from the distributed Sigma; needed once
+ *                      after create / ekf_fill_procedural / ekf_set_sigma_block / ekf_set_state.
+ *   ekf_shard_scan_*   one round of a scan update (slam.cpp:321-508): begin = prediction (when
+ *                      pose_dev != NULL; pass NULL on continuation rounds), speculative association,
+ *                      this rank's part of the needed Sigma columns -> exchange buffer; finish = the
+ *                      sequential measurement loop (replicated), the covariance pass over the owned
+ *                      rows.  *done_dev (device int) receives the number of sightings of the round
+ *                      that were applied: min(m, 24), or fewer when an association needed a landmark
+ *                      the speculation had not fetched - the caller then runs another round with the
+ *                      remaining sightings (xy_dev + 2 * done).  last_round = this round reaches the
+ *                      end of the scan (latches filter_previous_configuration, slam.cpp:508, when all
+ *                      of its sightings get applied).
+ * The ordinary ekf_scan / ekf_update_* entry points return EKF_ERR_INVALID on a sharded handle;
+ * ekf_get_sigma_block returns 0 for entries stored by another rank (sum over ranks = Sigma). */
+int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t *stored_doubles);
+int ekf_shard_sync_begin(ekf_filter *f, double **xchg_dev, int64_t *xchg_doubles);
+int ekf_shard_sync_finish(ekf_filter *f);
+int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const double *xy_dev,
+                         const int32_t *ids_dev, int32_t last_round, double **xchg_dev, int64_t *xchg_doubles);
+int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, double *pose_out_dev,
+                          int32_t *count_dev);
+
 /* ---- batched mode: B independent small filters, one CTA each, Sigma in shared memory ---------
  * (BASELINE config 3).  Each filter runs the whole sensor callback of the reference
  * (slam.cpp:184-291 known / :321-508 unknown association) per step.  Buffers are struct-of-arrays
