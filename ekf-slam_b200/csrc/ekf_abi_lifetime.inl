@@ -103,11 +103,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   // Pp (n_pad rows) and D (N blocks) share one allocation: a sharded handle all-reduces both at once
   CKC(cudaMalloc(&f->Pp, ((size_t)f->n_pad + f->N) * sizeof(double4)));
   f->D = f->Pp + f->n_pad;
-  if (f->sharded) {
-    CKC(cudaMalloc(&f->cols, (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double)));
-    CKC(cudaMalloc(&f->guess, kMaxChunkM * sizeof(int)));
-    CKC(cudaMalloc(&f->done_dev, sizeof(int)));
-  }
+  // the exchange buffers of the shard protocol are allocated on first use (ekf_abi_shard.inl)
   CKC(cudaMalloc(&f->cnt, sizeof(int)));
   CKC(cudaMalloc(&f->status, sizeof(int)));
   CKC(cudaMalloc(&f->prev_xy, 2 * sizeof(double)));

@@ -56,6 +56,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
 int scan_device(ekf_filter *f, const double *pose_dev, int m, const double *xy_dev, const int32_t *ids_dev,
                 const uint8_t *action_dev, int32_t *assoc_dev, double *pose_out_dev, int *cnt_out_dev) {
   if (f->sharded) return EKF_ERR_INVALID;   // a row shard cannot run a scan alone: ekf_shard_scan_*
+  f->side_valid = false;                    // this path re-extracts Pp / D from Sigma every scan
   int t0 = 0;
   bool first = true;
   do {

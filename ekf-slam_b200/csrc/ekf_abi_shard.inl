@@ -2,7 +2,15 @@
 
 namespace {
 
-int shard_ok(ekf_filter *f) { return f && f->sharded; }
+// the shard protocol also runs on an unsharded handle (one shard that owns every row)
+int shard_ok(ekf_filter *f) { return f != nullptr; }
+
+int shard_buffers(ekf_filter *f) {
+  if (!f->cols) CK(f, cudaMalloc(&f->cols, (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double)));
+  if (!f->guess) CK(f, cudaMalloc(&f->guess, kMaxChunkM * sizeof(int)));
+  if (!f->done_dev) CK(f, cudaMalloc(&f->done_dev, sizeof(int)));
+  return EKF_OK;
+}
 
 }  // namespace
 
@@ -19,6 +27,8 @@ int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t 
 int ekf_shard_sync_begin(ekf_filter *f, double **xchg_dev, int64_t *xchg_doubles) {
   if (!shard_ok(f) || !xchg_dev || !xchg_doubles) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
+  int rcb = shard_buffers(f);
+  if (rcb != EKF_OK) return rcb;
   shard_side_extract_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
   f->launches++;
   CK(f, cudaGetLastError());

@@ -53,22 +53,33 @@ def shard_bounds(n_landmarks: int, count: int):
 class _Driver:
     """round loop shared by both callers; subclasses provide handles() and exchange(list of (ptr, count))"""
 
-    def _setup(self, device):
+    def _setup(self, device, stream=None):
+        """every handle runs on ONE torch stream (self.stream), and so does every torch op of the driver"""
         self.device = device
-        self._done = torch.zeros(1, dtype=torch.int32, device=device)
-        self._cnt = torch.zeros(1, dtype=torch.int32, device=device)
-        self._pose_out = torch.zeros(3, dtype=torch.float64, device=device)
+        self.stream = stream if stream is not None else torch.cuda.Stream(device)
+        assert self.stream.cuda_stream != 0   # ekf_set_stream reads 0 as "the handle's own stream"
+        for h in self.handles():
+            h.set_stream(self.stream.cuda_stream)
+        with torch.cuda.stream(self.stream):
+            self._done = torch.zeros(1, dtype=torch.int32, device=device)
+            self._cnt = torch.zeros(1, dtype=torch.int32, device=device)
+            self._pose_out = torch.zeros(3, dtype=torch.float64, device=device)
 
     def sync(self):
-        bufs = [h.shard_sync_begin() for h in self.handles()]
-        self.exchange(bufs)
-        for h in self.handles():
-            h.shard_sync_finish()
+        with torch.cuda.stream(self.stream):
+            bufs = [h.shard_sync_begin() for h in self.handles()]
+            self.exchange(bufs)
+            for h in self.handles():
+                h.shard_sync_finish()
 
     def scan_dev(self, pose_t, xy_t, assoc_t, ids_t=None, check: bool = True):
         """One scan from device tensors: pose_t [3], xy_t [m, 2], assoc_t int32 [m] (written).
         With check=False a single round is enqueued without reading `done` back (fully asynchronous;
         valid when m <= 24 and the speculation holds - inspect self._done afterwards)."""
+        with torch.cuda.stream(self.stream):
+            return self._scan_dev(pose_t, xy_t, assoc_t, ids_t, check)
+
+    def _scan_dev(self, pose_t, xy_t, assoc_t, ids_t, check):
         m = xy_t.shape[0]
         t0, first, rounds = 0, True, 0
         while t0 < m:
@@ -94,12 +105,14 @@ class _Driver:
     def scan(self, pose, xy, ids=None):
         """host arrays in, (assoc, count, pose_after, rounds) out"""
         xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
-        pose_t = torch.from_numpy(np.ascontiguousarray(pose, dtype=np.float64)).to(self.device)
-        xy_t = torch.from_numpy(xy).to(self.device)
-        ids_t = None if ids is None else torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int32)).to(self.device)
-        assoc_t = torch.full((len(xy),), -7, dtype=torch.int32, device=self.device)
-        rounds = self.scan_dev(pose_t, xy_t, assoc_t, ids_t)
-        return assoc_t.cpu().numpy(), int(self._cnt.item()), self._pose_out.cpu().numpy(), rounds
+        with torch.cuda.stream(self.stream):
+            pose_t = torch.from_numpy(np.ascontiguousarray(pose, dtype=np.float64)).to(self.device)
+            xy_t = torch.from_numpy(xy).to(self.device)
+            ids_t = None if ids is None else \
+                torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int32)).to(self.device)
+            assoc_t = torch.full((len(xy),), -7, dtype=torch.int32, device=self.device)
+            rounds = self._scan_dev(pose_t, xy_t, assoc_t, ids_t, True)
+            return assoc_t.cpu().numpy(), int(self._cnt.item()), self._pose_out.cpu().numpy(), rounds
 
 
 class LocalShards(_Driver):
@@ -110,27 +123,17 @@ class LocalShards(_Driver):
                    for r in range(shards)]
         self._setup(torch.device("cuda", device_index))
         self.n = self.hs[0].n
-        stream = torch.cuda.current_stream(self.device)
-        if stream.cuda_stream != 0:
-            for h in self.hs:
-                h.set_stream(stream.cuda_stream)
-        self._own_stream = stream.cuda_stream == 0
 
     def handles(self):
         return self.hs
 
     def exchange(self, bufs):
-        if self._own_stream:            # handles run on their own streams: order by synchronising
-            for h in self.hs:
-                h.synchronize()
         ts = [alias(p, c, self.device) for (p, c) in bufs]
         total = ts[0].clone()
         for t in ts[1:]:
             total += t
         for t in ts:
             t.copy_(total)
-        if self._own_stream:
-            torch.cuda.synchronize(self.device)
 
     # fixtures applied to every shard
     def fill_procedural(self, seed, count, grid_w):
@@ -162,12 +165,8 @@ class ShardedEkf(_Driver):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.h = EkfSlam(n_landmarks=n_landmarks, device=device_index, shard_rank=rank, shard_count=world, **kw)
-        self._setup(torch.device("cuda", device_index))
+        self._setup(torch.device("cuda", device_index), stream)
         self.n = self.h.n
-        stream = stream or torch.cuda.current_stream(self.device)
-        if stream.cuda_stream == 0:
-            raise ValueError("ShardedEkf needs a non-default torch stream (ekf_set_stream reads 0 as 'own stream')")
-        self.h.set_stream(stream.cuda_stream)
 
     def handles(self):
         return [self.h]

@@ -77,12 +77,12 @@ def test_sharded_scan_longer_than_one_round():
 
 
 def test_failed_speculation_resumes_with_identical_results():
-    """fault injection: the columns of sighting 5 are not fetched, the round stops there and the
-    driver runs a second round for the rest - same numbers as ever."""
+    """fault injection: the columns of sighting 5 of every round are not fetched; each round stops there
+    and the driver continues with the rest (20 sightings -> rounds of 5, 5, 5, 5) - same numbers as ever."""
     os.environ["EKF_SHARD_DROP_GUESS"] = "5"
     try:
         g, o, grid_w = _pair(300, 290, 3)
-        _drive(g, o, 290, grid_w, 20, 2, expect_rounds=2)
+        _drive(g, o, 290, grid_w, 20, 2, expect_rounds=4)
         g.close(); o.close()
     finally:
         del os.environ["EKF_SHARD_DROP_GUESS"]
