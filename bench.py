@@ -10,8 +10,10 @@ association, gain, state update) + the fused covariance pass (BASELINE.json metr
 through the host-buffer C ABI call (H2D + D2H inside), `roofline` for the dominant kernel
 (ekf_downdate_kernel, HBM-bound), `cpu_baseline` = oracle B ("port") on the host cores.
 
-N > 1 GPUs (round 1): independent replicas, one filter per GPU, no collective on the data path
-("weak" scaling); the row-sharded single map is DESIGN.md section "multi-GPU" (next).
+N > 1 GPUs: the SAME single map, Sigma row-sharded over the ranks (equal-area split, replicated
+sequential phase, one NCCL sum-all-reduce of the speculated column panel per scan):
+"strong" scaling.  The "batched" sub-object is BASELINE configs[2] (65,536 independent 20-landmark filters
+per GPU, one CTA each, no communication; weak scaling).
 """
 from __future__ import annotations
 
@@ -44,6 +46,11 @@ def parse_args():
     ap.add_argument("--m", type=int, default=20)
     ap.add_argument("--seed", type=int, default=7)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-batched", action="store_true", help="skip the batched-filters section")
+    ap.add_argument("--batch-filters", type=int, default=65536, help="filters per GPU (BASELINE configs[2])")
+    ap.add_argument("--batch-landmarks", type=int, default=20)
+    ap.add_argument("--batch-m", type=int, default=20)
+    ap.add_argument("--batch-steps", type=int, default=10)
     ap.add_argument("--cpu-sample-meas", type=int, default=2,
                     help="measurements of one scan the CPU baseline actually runs (scaled to m)")
     return ap.parse_args()
@@ -211,6 +218,80 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def bench_batched(args, torch, ekf, stream, local, world, dist):
+    """BASELINE config 3: independent small filters, one CTA each, sharded over the ranks with no
+    communication (weak scaling: `--batch-filters` filters PER GPU).  Returns the sub-object that goes
+    into the JSON line under "batched"."""
+    from ekf_slam_b200 import synth
+    B, N, m = args.batch_filters, args.batch_landmarks, args.batch_m
+    rank = int(os.environ.get("RANK", "0"))
+    K, W = args.batch_steps, 4
+    g = ekf.EkfBatch(B, n_landmarks=N, device=local)
+    g.set_stream(stream.cuda_stream)
+    fields = synth.batch_fields(B, N, seed=args.seed + 17 * rank)
+    rng = np.random.default_rng(args.seed + 1000 + rank)
+    T = W + 2 * K
+    h_pose, h_xy, d_pose, d_xy, ids = [], [], [], [], []
+    for s in range(T):
+        p = synth.batch_pose(B, s)
+        xy, order = synth.batch_scan(fields, p, rng, m=N if s < 2 else m)   # the first scans map every landmark
+        h_pose.append(p); h_xy.append(xy); ids.append(order)
+        d_pose.append(torch.from_numpy(p).cuda()); d_xy.append(torch.from_numpy(xy).cuda())
+    d_assoc = torch.zeros((T, B, N), dtype=torch.int32, device="cuda")
+    d_cnt = torch.zeros(B, dtype=torch.int32, device="cuda")
+
+    def step(s):
+        g.step_dev(d_pose[s].data_ptr(), d_xy[s].shape[1], d_xy[s].data_ptr(), 0, 0, d_assoc[s].data_ptr(),
+                   d_cnt.data_ptr(), 0)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for s in range(W):
+        step(s)
+    l0 = g.launch_count()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for s in range(W, W + K):
+        step(s)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = g.launch_count() - l0
+    # the landmark numbering of a filter is the order of its first scan: ids[0]; expected association of
+    # a later sighting of true landmark L is the position of L in that order
+    pos = np.empty_like(ids[0]); np.put_along_axis(pos, ids[0], np.arange(N, dtype=np.int32)[None].repeat(B, 0), axis=1)
+    ok = True
+    for s in (W, W + K - 1):
+        exp = np.take_along_axis(pos, ids[s], axis=1)
+        ok = ok and bool((d_assoc[s, :, :ids[s].shape[1]].cpu().numpy() == exp).all())
+    ok = ok and g.last_status() == 0 and int(d_cnt.min()) == N
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(W + K, W + 2 * K):
+        g.step(h_pose[s], h_xy[s])
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1000.0
+    tt = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(tt[0]), float(tt[1])
+    byt = g.step_bytes(m)
+    g.close()
+    peak, _ = peaks()
+    value = world * B * K / (ms / 1000.0)
+    return {"metric": "ekf_batched_filter_steps_per_s", "value": value, "unit": "filter-steps/s",
+            "filters_per_gpu": B, "landmarks": N, "m": m, "steps": K, "ms_per_step": ms / K, "scaling": "weak",
+            "association_bit_exact_vs_expected_ids": ok, "gpu_launches": int(launches),
+            "bytes_per_filter_step": byt, "hbm_frac": (value / world * byt / 1e9) / peak,
+            "e2e": {"value": world * B * K / (e2e_ms / 1000.0), "unit": "filter-steps/s",
+                    "h2d_bytes_per_step": B * (24 + 16 * m), "d2h_bytes_per_step": B * (4 * m + 4 + 24) + 4}}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -226,26 +307,39 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N, m, K, W = args.landmarks, args.m, args.steps, args.warmup
     n = 3 + 2 * N
-    f = ekf.EkfSlam(n_landmarks=N, device=local, max_scan=m)
     side = int(np.ceil(np.sqrt(N)))
-    f.fill_procedural(args.seed + rank, N, side)
-    state0 = f.state()
-    n_scans = 2 * (W + K)
-    poses, xy, ids = make_workload(state0, N, m, n_scans, args.seed + 100 + rank)
-    f.set_previous_xy(poses[0][1], poses[0][2])
-    # a non-default stream: the legacy default stream's handle is NULL, which ekf_set_stream reads
-    # as "use the handle's own stream" - the timing events must sit on the stream the kernels use
+    # a non-default stream: the legacy default stream's handle is NULL, which ekf_set_stream reads as
+    # "use the handle's own stream" - the timing events must sit on the stream the kernels use
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
-    f.set_stream(stream.cuda_stream)
+    sharded = world > 1
+    if sharded:
+        # ONE map row-sharded over the ranks (BASELINE configs[3] "row-sharded Sigma"): strong scaling
+        from ekf_slam_b200 import shard
+        drv = shard.ShardedEkf(N, rank, world, local, stream=stream, max_scan=m)
+        f = drv.h
+        f.fill_procedural(args.seed, N, side)       # same seed everywhere: every rank fills its own rows
+        drv.sync()
+    else:
+        f = ekf.EkfSlam(n_landmarks=N, device=local, max_scan=m)
+        f.set_stream(stream.cuda_stream)
+        f.fill_procedural(args.seed, N, side)
+    state0 = f.state()
+    n_scans = 2 * (W + K)
+    poses, xy, ids = make_workload(state0, N, m, n_scans, args.seed + 100)
+    f.set_previous_xy(poses[0][1], poses[0][2])
     d_pose = torch.from_numpy(poses).cuda()
     d_xy = torch.from_numpy(xy).cuda()
     d_assoc = torch.full((n_scans, m), -9, dtype=torch.int32, device="cuda")
+    d_done = torch.full((n_scans,), m, dtype=torch.int32, device="cuda")
     stored, n_pad = f.storage()
 
     def scan_dev(s):
-        f.scan_dev(d_pose[s].data_ptr(), m, d_xy[s].data_ptr(), 0, 0, d_assoc[s].data_ptr())
+        if sharded:
+            drv.scan_dev(d_pose[s], d_xy[s], d_assoc[s], check=False, done_t=d_done[s:s + 1])
+        else:
+            f.scan_dev(d_pose[s].data_ptr(), m, d_xy[s].data_ptr(), 0, 0, d_assoc[s].data_ptr())
 
     def barrier():
         torch.cuda.synchronize()
@@ -277,12 +371,15 @@ def run_ours(args):
     f.enable_timing(0)
     status = f.last_status()
 
-    # ---- end to end through the host-buffer ABI call (`e2e`) -----------------------------------
+    # ---- end to end through the host-buffer call (`e2e`) ---------------------------------------
     e_assoc = []
     barrier()
     t2 = time.perf_counter()
     for s in range(W + K, W + 2 * K):
-        a, cnt, _ = f.scan(poses[s], xy[s])
+        if sharded:
+            a, cnt, _, _ = drv.scan(poses[s], xy[s])
+        else:
+            a, cnt, _ = f.scan(poses[s], xy[s])
         e_assoc.append(a)
     barrier()
     t3 = time.perf_counter()
@@ -293,43 +390,64 @@ def run_ours(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     ms_total, e2e_ms = float(tt[0]), float(tt[1])
     assoc_dev = d_assoc[W:W + K].cpu().numpy()
-    assoc_ok = bool((assoc_dev == ids[W:W + K]).all() and
+    assoc_ok = bool((assoc_dev == ids[W:W + K]).all() and bool((d_done[:W + K] == m).all()) and
                     all((np.asarray(a) == ids[W + K + i]).all() for i, a in enumerate(e_assoc)) and status == 0)
     ok = torch.tensor([1 if assoc_ok else 0], device="cuda")
     if world > 1:
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    stored_all = torch.tensor([float(stored)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(stored_all, op=dist.ReduceOp.SUM)
+
+    batched = None
+    if not args.no_batched:
+        batched = bench_batched(args, torch, ekf, stream, local, world, dist)
+
     if rank != 0:
-        f.close()
+        (drv if sharded else f).close()
         if world > 1:
             dist.destroy_process_group()
         return
 
-    value = world * K / (ms_total / 1000.0)
-    e2e_value = world * K / (e2e_ms / 1000.0)
+    # one scan update of ONE map per step: with several GPUs the same map is row-sharded (strong scaling)
+    value = K / (ms_total / 1000.0)
+    e2e_value = K / (e2e_ms / 1000.0)
     b_scan, b_pass = algorithmic_bytes(n, m)
     peak, peak_src = peaks()
     dd_avg_ms = float(np.mean(dd_ms)) if len(dd_ms) else float("nan")
-    achieved = b_pass / (dd_avg_ms * 1e-3) / 1e9
+    # the covariance pass of this rank streams its share of the triangle: algorithmic bytes per launch
+    b_pass_rank = b_pass * stored / float(stored_all.item())
+    achieved = b_pass_rank / (dd_avg_ms * 1e-3) / 1e9
+    traffic = None
+    prof = os.path.join(ROOT, "profiles", "downdate_traffic.json")
+    if os.path.exists(prof) and world == 1 and N == 10000 and m == 20:
+        with open(prof) as fh:
+            traffic = json.load(fh).get("dram_bytes_per_launch")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong" if sharded else "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"single large map N={N} landmarks (n={n}), {m} measurements/scan, unknown "
                                "association, all landmarks mapped (BASELINE.json configs[3])",
-                   "landmarks": N, "m": m, "parallelism": "1 filter per GPU (replicas)" if world > 1 else "1 GPU",
-                   "l2": f"inputs larger than L2: Sigma triangle = {stored * 8 / 1e9:.2f} GB streamed per scan",
+                   "landmarks": N, "m": m,
+                   "parallelism": (f"one map, Sigma row-sharded over {world} GPUs (equal-area), one NCCL sum-all-reduce "
+                                   f"of the {m}x{n_pad}x2 column panel per scan") if sharded else "1 GPU",
+                   "l2": f"inputs larger than L2: Sigma triangle = {float(stored_all.item()) * 8 / 1e9:.2f} GB streamed "
+                         "per scan",
                    "association_bit_exact_vs_expected_ids": bool(ok.item())},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 + 16 * m, "d2h_bytes_per_step": 32 + 4 * m,
                 "ms_per_step": e2e_ms / K},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "ekf_downdate_kernel", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": b_pass, "avg_launch_ms": dd_avg_ms,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": b_pass_rank, "avg_launch_ms": dd_avg_ms,
                      "seq_phase_avg_ms": float(np.mean(seq_ms)) if len(seq_ms) else None,
-                     "scan_frac_of_hbm_roofline": (b_scan * value / world / 1e9) / peak},
+                     "scan_frac_of_hbm_roofline": (b_scan * value / 1e9) / (peak * world)},
     }
-    if not args.no_cpu_baseline:
+    if batched is not None:
+        line["batched"] = batched
+    if not args.no_cpu_baseline and world == 1:
         def fill_rows(sig):
             rows = 2048
             for i0 in range(0, n, rows):
@@ -342,7 +460,7 @@ def run_ours(args):
         o.close()
         line["cpu_baseline"] = {"value": 1.0 / secs, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": cpu_desc(N, m, args.cpu_sample_meas, 1)}
-    f.close()
+    (drv if sharded else f).close()
     if world > 1:
         dist.destroy_process_group()
     print(json.dumps(line))

@@ -72,14 +72,15 @@ class _Driver:
             for h in self.handles():
                 h.shard_sync_finish()
 
-    def scan_dev(self, pose_t, xy_t, assoc_t, ids_t=None, check: bool = True):
+    def scan_dev(self, pose_t, xy_t, assoc_t, ids_t=None, check: bool = True, done_t=None):
         """One scan from device tensors: pose_t [3], xy_t [m, 2], assoc_t int32 [m] (written).
         With check=False a single round is enqueued without reading `done` back (fully asynchronous;
         valid when m <= 24 and the speculation holds - inspect self._done afterwards)."""
         with torch.cuda.stream(self.stream):
-            return self._scan_dev(pose_t, xy_t, assoc_t, ids_t, check)
+            return self._scan_dev(pose_t, xy_t, assoc_t, ids_t, check, done_t)
 
-    def _scan_dev(self, pose_t, xy_t, assoc_t, ids_t, check):
+    def _scan_dev(self, pose_t, xy_t, assoc_t, ids_t, check, done_t=None):
+        done_t = self._done if done_t is None else done_t
         m = xy_t.shape[0]
         t0, first, rounds = 0, True, 0
         while t0 < m:
@@ -90,13 +91,13 @@ class _Driver:
                     for h in self.handles()]
             self.exchange(bufs)
             for h in self.handles():
-                h.shard_scan_finish(assoc_t[t0:].data_ptr(), self._done.data_ptr(), self._pose_out.data_ptr(),
+                h.shard_scan_finish(assoc_t[t0:].data_ptr(), done_t.data_ptr(), self._pose_out.data_ptr(),
                                     self._cnt.data_ptr())
             rounds += 1
             first = False
             if not check:
                 return rounds
-            done = int(self._done.item())
+            done = int(done_t.item())
             if done == 0 and rounds > 4 * m + 4:
                 raise RuntimeError("sharded scan makes no progress")
             t0 += done
