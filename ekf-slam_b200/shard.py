@@ -178,3 +178,8 @@ class ShardedEkf(_Driver):
 
     def close(self):
         self.h.close()
+
+
+def filter_range(n_filters: int, rank: int, world: int):
+    """[lo, hi) of the independent filters rank `rank` steps in batched mode (no communication)."""
+    return n_filters * rank // world, n_filters * (rank + 1) // world
