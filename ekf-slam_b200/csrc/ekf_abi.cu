@@ -61,9 +61,9 @@ struct ekf_filter {
   int64_t launches = 0;
   int seq_grid = 1;
   int dd_grid = 1;
-  int dd_prefetch = 1;
+  int dd_prefetch = 0;
   int dd_ctas = 2;
-  int dd_variant = 1;      // 0: <64 rows, register prefetch>, 1 CTA / SM;  1: <32 rows>, 3 CTAs / SM
+  int dd_variant = 2;      // 0: <64 rows, register prefetch>, 1 CTA / SM;  1: <32 rows>, 3 CTAs / SM
   int latched = EKF_OK;
   std::string cuda_err;
 };

@@ -117,26 +117,32 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   f->seq_grid = seq_blocks < max_seq ? seq_blocks : max_seq;
   f->dd_grid = env_int("EKF_DD_BLOCKS", f->num_sms);
   if (f->dd_grid < 1) f->dd_grid = 1;
-  f->dd_prefetch = env_int("EKF_DD_PREFETCH", 1);
-  f->dd_variant = env_int("EKF_DD_VARIANT", 1);
+  f->dd_prefetch = env_int("EKF_DD_PREFETCH", 0);
+  f->dd_variant = env_int("EKF_DD_VARIANT", 2);
   f->dd_ctas = env_int("EKF_DD_CTAS", 2);
   if (f->dd_ctas < 1) f->dd_ctas = 1;
   if (f->dd_prefetch < 0) f->dd_prefetch = 0;
   CKC(cudaMalloc(&f->slot_d, 2 * (size_t)f->num_sms * sizeof(double)));
   CKC(cudaMalloc(&f->slot_k, 2 * (size_t)f->num_sms * sizeof(int)));
   CKC(cudaMalloc(&f->slot_rec, 2 * (size_t)f->num_sms * kRecStride * sizeof(double)));
-  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(64, kMaxK2)));
-  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)dd_smem_bytes(64, kMaxK2)));
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(32, kMaxK2)));
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)dd_smem_bytes(32, kMaxK2)));
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<32, 2>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                           cudaSharedmemCarveoutMaxShared));
   // several CTAs of the <32> shape share an SM only if the SM is configured with (nearly) all of its
   // L1 / shared storage as shared memory
-  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<32, false>, cudaFuncAttributePreferredSharedMemoryCarveout,
+  CKC(cudaFuncSetAttribute(ekf_downdate_kernel<32, 0>, cudaFuncAttributePreferredSharedMemoryCarveout,
                            cudaSharedmemCarveoutMaxShared));
   if (env_int("EKF_DEBUG", 0)) {
     int occ = 0;
     for (int k2 = 8; k2 <= kMaxK2; k2 += 8) {
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ekf_downdate_kernel<32, false>, dd_threads(32),
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ekf_downdate_kernel<32, 0>, dd_threads(32),
                                                     dd_smem_bytes(32, k2));
       fprintf(stderr, "ekf: downdate<32> k2=%d smem=%zu B -> %d CTAs / SM\n", k2, dd_smem_bytes(32, k2), occ);
     }

@@ -34,16 +34,22 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
     dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;  // whole k-steps; pad columns are zero
     dp.lay = f->lay; dp.row_begin = f->lay.rb; dp.row_end = f->lay.re;
     dp.prefetch_ahead = f->dd_prefetch;
-    if (f->dd_variant == 0) {
+    if (f->dd_variant == 0 || f->dd_variant == 2) {
       dp.total_chunks = dd_total_chunks(64, dp.row_begin, dp.row_end);
       long long grid = f->dd_grid;
       if (grid > dp.total_chunks) grid = dp.total_chunks;
-      ekf_downdate_kernel<64, true><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
+      if (f->dd_variant == 0)
+        ekf_downdate_kernel<64, 1><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
+      else
+        ekf_downdate_kernel<64, 2><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
     } else {
       dp.total_chunks = dd_total_chunks(32, dp.row_begin, dp.row_end);
       long long grid = (long long)f->dd_grid * f->dd_ctas;
       if (grid > dp.total_chunks) grid = dp.total_chunks;
-      ekf_downdate_kernel<32, false><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
+      if (f->dd_variant == 3)
+        ekf_downdate_kernel<32, 2><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
+      else
+        ekf_downdate_kernel<32, 0><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
     }
     f->launches++;
     CK(f, cudaGetLastError());

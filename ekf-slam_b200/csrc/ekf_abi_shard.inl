@@ -115,7 +115,7 @@ int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, 
   dp.total_chunks = dd_total_chunks(32, dp.row_begin, dp.row_end);
   long long grid = (long long)f->dd_grid * f->dd_ctas;
   if (grid > dp.total_chunks) grid = dp.total_chunks;
-  ekf_downdate_kernel<32, false><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
+  ekf_downdate_kernel<32, 0><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
   shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
   f->launches += 2;
   CK(f, cudaGetLastError());

@@ -154,8 +154,8 @@ __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double
 }
 
 // k2 must be a multiple of 4 (the sequential kernel zero-fills the pad columns of an odd scan).
-template <int CR, bool PF>
-__global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kernel(const DdParams p) {
+template <int CR, int PF>
+__global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) ekf_downdate_kernel(const DdParams p) {
   constexpr int kComputeWarps = CR / 8;            // each warp owns a 32 x 32 tile of the chunk
   constexpr int kComputeThreads = kComputeWarps * 32;
   constexpr int kVBlocks = CR / EKF_PBLK;          // 32-row panel blocks per chunk
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kerne
     double *out = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
     const int curJ = cur.J;
     dd_advance(cur, CR, p.row_begin, p.row_end);
-    if (PF) {
+    if (PF == 1) {
       if (it + 1 < n_chunks) {       // prefetch the next chunk's tile into the second register set
         const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
 #pragma unroll
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kerne
             ld256(base + toff[i] + 16 * jj, cn[i][2 * jj][0], cn[i][2 * jj][1], cn[i][2 * jj + 1][0],
                   cn[i][2 * jj + 1][1]);
       }
-    } else {
+    } else if (PF == 0) {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -278,8 +278,34 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? 1 : 3) ekf_downdate_kerne
 
     const double *va = s_v + (s * kVBlocks + wr) * blk_elems + lane;
     const double *wb = s_w + wc * blk_elems + lane;
+    int ks0 = 0;
+    if (PF == 2) {
+      // first k-step, THEN the register prefetch of the next chunk: every accumulator's load has been
+      // consumed before new loads are issued, so the new loads cannot hold back the DMMAs of this chunk
+      {
+        double a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = -va[i * 32];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = wb[j * 32];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dmma884(c[i][j][0], c[i][j][1], a[i], b[j]);
+      }
+      ks0 = 1;
+      if (it + 1 < n_chunks) {
+        const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+            ld256(base + toff[i] + 16 * jj, cn[i][2 * jj][0], cn[i][2 * jj][1], cn[i][2 * jj + 1][0],
+                  cn[i][2 * jj + 1][1]);
+      }
+    }
 #pragma unroll 2
-    for (int ks = 0; ks < ksteps; ++ks) {
+    for (int ks = ks0; ks < ksteps; ++ks) {
       double a[4], b[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) a[i] = -va[ks * 128 + i * 32];
