@@ -215,7 +215,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    _emit(_OUT, json.dumps(line))
 
 
 def bench_batched(args, torch, ekf, stream, local, world, dist):
@@ -463,11 +463,27 @@ def run_ours(args):
     (drv if sharded else f).close()
     if world > 1:
         dist.destroy_process_group()
-    print(json.dumps(line))
+    _emit(_OUT, json.dumps(line))
+
+
+def _quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries (NCCL prints its version banner to stdout) must
+    not add to it: everything written to fd 1 while the benchmark runs goes to stderr instead; the JSON
+    line is written to the saved descriptor."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    return saved
+
+
+def _emit(saved_fd, text):
+    sys.stdout.flush()
+    os.write(saved_fd, (text + "\n").encode())
 
 
 if __name__ == "__main__":
     a = parse_args()
+    _OUT = _quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

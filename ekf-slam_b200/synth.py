@@ -30,6 +30,7 @@ class Scan:
     ids: np.ndarray        # (m,) landmark ids (known association) - ignored by the unknown path
     action: np.ndarray     # (m,) MARKER_ADD / MARKER_DELETE
     truth: tuple = (0.0, 0.0, 0.0)
+    wheels: tuple = (0.0, 0.0)   # encoder angles (left, right) that produced `odom` (joint_states)
 
 
 def _compose(a, b):
@@ -111,7 +112,7 @@ def circle_drive(n_scans=300, seed=0, landmarks=BASIC_WORLD, radius=0.3, speed=0
             xy = [xy[p] for p in perm]; ids = [ids[p] for p in perm]; act = [act[p] for p in perm]
         scans.append(Scan(odom=odom_drive.cfg, xy=np.array(xy, dtype=np.float64).reshape(-1, 2),
                           ids=np.array(ids, dtype=np.int32), action=np.array(act, dtype=np.uint8),
-                          truth=pose))
+                          truth=pose, wheels=(enc_l, enc_r)))
     return scans
 
 

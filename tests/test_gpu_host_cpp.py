@@ -1,0 +1,50 @@
+"""The C++ host path: nuslam::SlamCore (ekf-slam_b200/host/nuslam/slam_core.hpp, the node-shell adapter
+of SURVEY.md 8(f) N3) linked against the C-ABI library, fed with wheel angles and marker lists like
+the reference's callbacks, against oracle A driven by the same trace."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from _harness import ekf_slam_b200, run_literal, synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build(tmp_path):
+    exe = str(tmp_path / "slam_core_replay")
+    pkg = os.path.join(ROOT, "ekf-slam_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-pedantic", "-ffp-contract=off",
+                           "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(pkg, "host"),
+                           os.path.join(ROOT, "tests", "cpp", "slam_core_replay.cpp"), "-o", exe,
+                           "-L" + pkg, "-lekf_slam_b200", "-Wl,-rpath," + pkg])
+    return exe
+
+
+@pytest.mark.parametrize("known", [True, False])
+def test_slam_core_replay_matches_oracle_a(tmp_path, known):
+    if not os.path.exists(ekf_slam_b200.LIB_PATH):
+        ekf_slam_b200.build()
+    exe = _build(tmp_path)
+    scans = synth.circle_drive(n_scans=60, seed=21) if known else \
+        synth.circle_drive(n_scans=60, seed=22, drop_out_of_range=True, shuffle=True)
+    scans = [s for s in scans if len(s.xy)]
+    lines = [f"{int(known)} 50 {len(scans)}"]
+    for s in scans:
+        lines.append(f"{s.wheels[0]!r} {s.wheels[1]!r} {len(s.xy)}")
+        for i, (x, y), a in zip(s.ids, s.xy, s.action):
+            lines.append(f"{int(i)} {float(x)!r} {float(y)!r} {int(a)}")
+    out = subprocess.run([exe], input="\n".join(lines) + "\n", capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    rows = out.stdout.strip().split("\n")
+    aL, sL, SL, cL = run_literal(scans, known)
+    last = rows[len(scans) - 1].split()
+    pose = np.array([float(v) for v in last[:3]])
+    assert np.allclose(pose, sL[:3], rtol=0, atol=1e-9)
+    if not known:
+        assert int(last[3]) == cL
+        got = [[int(v) for v in r.split()[4:]] for r in rows[:len(scans)]]
+        assert got == [list(map(int, a)) for a in aL]
+    assert rows[-1].startswith("MAPODOM")
