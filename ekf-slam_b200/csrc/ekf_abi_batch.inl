@@ -34,7 +34,8 @@ int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, con
   p.sigma = b->sigma; p.mu = b->mu; p.prev = b->prev; p.cnt = b->cnt; p.status = b->status;
   p.pose = poses; p.xy = xy; p.ids = ids; p.m_count = m_count; p.m = m;
   p.assoc_out = assoc; p.cnt_out = count; p.pose_out = pose_out;
-  ekf_batch_kernel<<<b->B, kBatchThreads, batch_smem_bytes(b->n), b->stream>>>(p);
+  if (batch_smem_bytes(b->n, m) > 200 * 1024) return EKF_ERR_INVALID;   // m beyond the per-CTA shared memory
+  ekf_batch_kernel<<<b->B, kBatchThreads, batch_smem_bytes(b->n, m), b->stream>>>(p);
   b->launches++;
   CKB(b, cudaGetLastError());
   return EKF_OK;
@@ -131,7 +132,7 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
   b->launches++;
   CKC(cudaGetLastError());
   CKC(cudaFuncSetAttribute(ekf_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)batch_smem_bytes(131)));
+                           200 * 1024));
   CKC(cudaFuncSetAttribute(ekf_batch_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                            cudaSharedmemCarveoutMaxShared));
   CKC(cudaStreamSynchronize(b->stream));

@@ -43,9 +43,9 @@ struct BatchParams {
 constexpr int kBatchThreads = 32;
 constexpr int kBatchErrCapacity = 2, kBatchErrBadId = 4;   // ekf_status values
 
-__host__ __device__ inline size_t batch_smem_bytes(int n) {
+__host__ __device__ inline size_t batch_smem_bytes(int n, int m) {
   const size_t tri = (size_t)n * (n + 1) / 2;
-  return (tri + (size_t)n + 4 * (size_t)n + 8) * sizeof(double);
+  return (tri + (size_t)n + 4 * (size_t)n + 2 * (size_t)m + 8) * sizeof(double);
 }
 
 // Sigma_0 = diag(0, 0, 0, prior * I_2N) for every filter: slam.cpp:128-132
@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
   double *mu = S + tri;           // state
   double2 *G = reinterpret_cast<double2 *>(mu + n + (n & 1));   // G = Sigma H^T   (n x 2)
   double2 *K = G + n;                                           // K = G S^-1      (n x 2)
+  double *ZP = reinterpret_cast<double *>(K + n);               // polar sightings (m x 2)
   const int f = blockIdx.x;
   const int lane = threadIdx.x;
   if (f >= p.B) return;
@@ -123,9 +124,14 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
   const int mf = p.m_count ? min(p.m_count[f], p.m) : p.m;
   const bool unknown = (p.ids == nullptr);
   int err = 0;
+  // polar form of every sighting of the scan, one lane each (slam.cpp:345-347 does not depend on the state)
+  for (int t = lane; t < mf; t += 32) {
+    const Polar z = to_polar(p.xy[((size_t)f * p.m + t) * 2], p.xy[((size_t)f * p.m + t) * 2 + 1]);
+    ZP[2 * t] = z.r; ZP[2 * t + 1] = z.phi;
+  }
+  __syncwarp();
   for (int t = 0; t < mf; ++t) {
-    const double mx = p.xy[((size_t)f * p.m + t) * 2], my = p.xy[((size_t)f * p.m + t) * 2 + 1];
-    const Polar z = to_polar(mx, my);                          // slam.cpp:345-347
+    const Polar z{ZP[2 * t], ZP[2 * t + 1]};
     const double th = mu[0], px = mu[1], py = mu[2];
     double pb[3][3];
 #pragma unroll

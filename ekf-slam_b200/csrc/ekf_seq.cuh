@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   __shared__ int s_cnt;
   __shared__ double s_pred[2];    // (-dy, dx)
   __shared__ double s_pb0[3][3];  // pose block right after the prediction (what Sigma_0 holds)
+  __shared__ double s_zr[kMaxChunkM], s_zphi[kMaxChunkM];   // polar form of the scan's sightings
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -225,9 +226,15 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   const bool unknown = (p.ids == nullptr);
   const int G = (int)gridDim.x;
   int done = p.m;
+  // slam.cpp:345-347 for every sighting at once (it does not depend on the state): keeps sqrt / atan2
+  // out of the per-measurement dependent chain
+  if (tid < p.m) {
+    const Polar zt = to_polar(p.xy[2 * tid], p.xy[2 * tid + 1]);
+    s_zr[tid] = zt.r; s_zphi[tid] = zt.phi;
+  }
+  __syncthreads();
   for (int t = 0; t < p.m; ++t) {
-    const double mx = p.xy[2 * t], my = p.xy[2 * t + 1];
-    const Polar z = to_polar(mx, my);                        // slam.cpp:345-347
+    const Polar z{s_zr[t], s_zphi[t]};
     const double th = s_ps[0], px = s_ps[1], py = s_ps[2];
     const int cnt = s_cnt;
     const int par = t & 1;
