@@ -96,6 +96,10 @@ def load() -> C.CDLL:
         "ekf_shard_sync_finish": (C.c_int, [vp]),
         "ekf_shard_scan_begin": (C.c_int, [vp, vp, i32, vp, vp, i32, C.POINTER(vp), i64p]),
         "ekf_shard_scan_finish": (C.c_int, [vp, vp, vp, vp, vp]),
+        "ekf_landmarks_create": (C.c_int, [i32, i32, i32, i32, C.POINTER(vp)]),
+        "ekf_landmarks_destroy": (C.c_int, [vp]),
+        "ekf_landmarks_detect": (C.c_int, [vp, i32, C.POINTER(C.c_float), C.c_float, C.c_float, C.c_double, dp, ip, ip]),
+        "ekf_landmarks_detect_dev": (C.c_int, [vp, i32, vp, C.c_float, C.c_float, C.c_double, vp, vp, vp, vp]),
         "ekf_batch_create": (C.c_int, [C.POINTER(EkfConfig), i32, C.POINTER(vp)]),
         "ekf_batch_destroy": (C.c_int, [vp]),
         "ekf_batch_set_stream": (C.c_int, [vp, vp]),
@@ -464,3 +468,40 @@ class EkfBatch:
         a = C.c_int64(0)
         self._check(self._L.ekf_batch_launch_count(self._h, C.byref(a)), "ekf_batch_launch_count")
         return int(a.value)
+
+
+class LandmarkExtractor:
+    """Batched LaserScan -> circle detections (ekf_landmarks_*; nuslam/src/landmarks.cpp:58-156)."""
+
+    def __init__(self, max_scans: int, n_ranges: int = 360, max_out: int = 16, device: int = -1):
+        self._L = load()
+        h = C.c_void_p()
+        rc = self._L.ekf_landmarks_create(max_scans, n_ranges, max_out, device, C.byref(h))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_landmarks_create")
+        self._h, self.max_scans, self.n_ranges, self.max_out = h, max_scans, n_ranges, max_out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ekf_landmarks_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def detect(self, ranges, angle_min: float, angle_increment: float, cluster_threshold: float = 0.2):
+        """ranges [n_scans, n_ranges] float32 -> (list of [k,3] arrays, status [n_scans])"""
+        ranges = np.ascontiguousarray(ranges, dtype=np.float32).reshape(-1, self.n_ranges)
+        ns = ranges.shape[0]
+        out = np.zeros((ns, self.max_out, 3))
+        cnt = np.zeros(ns, dtype=np.int32)
+        st = np.zeros(ns, dtype=np.int32)
+        rc = self._L.ekf_landmarks_detect(self._h, ns, ranges.ctypes.data_as(C.POINTER(C.c_float)),
+                                          C.c_float(angle_min), C.c_float(angle_increment), cluster_threshold,
+                                          _dp(out), _ip(cnt), _ip(st))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_landmarks_detect")
+        return [out[s, :min(int(cnt[s]), self.max_out)].copy() for s in range(ns)], st

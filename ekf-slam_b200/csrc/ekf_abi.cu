@@ -14,6 +14,7 @@
 #include "../../include/ekf_slam_b200.h"
 #include "ekf_batch.cuh"
 #include "ekf_downdate.cuh"
+#include "ekf_landmarks.cuh"
 #include "ekf_layout.h"
 #include "ekf_seq.cuh"
 #include "ekf_shard.cuh"
@@ -157,3 +158,4 @@ int env_int(const char *name, int dflt) {
 #include "ekf_abi_access.inl"
 #include "ekf_abi_batch.inl"
 #include "ekf_abi_shard.inl"
+#include "ekf_abi_landmarks.inl"

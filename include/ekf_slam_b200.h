@@ -63,6 +63,7 @@ typedef struct ekf_config {
 
 typedef struct ekf_filter ekf_filter;       /* one EKF (slam.cpp:659-676) */
 typedef struct ekf_batch ekf_batch;         /* B independent small EKFs, one CTA each */
+typedef struct ekf_landmarks ekf_landmarks; /* landmark extraction from LaserScans (the EKF's producer) */
 
 void ekf_default_config(ekf_config *cfg);
 const char *ekf_status_string(int status);
@@ -203,6 +204,23 @@ int ekf_batch_set_count(ekf_batch *b, int32_t index, int32_t count);
 int ekf_batch_set_previous_xy(ekf_batch *b, int32_t index, double x, double y);
 /* bytes of HBM traffic one filter-step moves */
 int ekf_batch_step_bytes(ekf_batch *b, int32_t m, int64_t *bytes);
+
+/* ---- landmark extraction: the step before the filter -------------------------
+ * A batch of LaserScans (float ranges, n_ranges beams each, as in sensor_msgs/LaserScan) ->
+ * per scan the circle detections (c_x, c_y, r) in the lidar-corrected robot frame, in cluster order:
+ * what nuslam's `landmarks` node publishes on green/detected_obstacles (nuslam/src/landmarks.cpp:58-156
+ * with turtlelib checkCircle / fitCircle, turtlelib/src/landmark_detection.cpp:5-135).  One CTA per scan.
+ * out_xyr[n_scans][max_out][3]; out_count[s] = detections of scan s (only the first max_out are stored);
+ * out_status[s] = 0, or EKF_ERR_EMPTY_SCAN when the scan has no range discontinuity at all (the
+ * reference throws at clusters.at(0), landmarks.cpp:95).  cluster_threshold = 0.2 in the reference. */
+int ekf_landmarks_create(int32_t max_scans, int32_t n_ranges, int32_t max_out, int32_t device, ekf_landmarks **out);
+int ekf_landmarks_destroy(ekf_landmarks *h);
+int ekf_landmarks_detect(ekf_landmarks *h, int32_t n_scans, const float *ranges, float angle_min,
+                         float angle_increment, double cluster_threshold, double *out_xyr, int32_t *out_count,
+                         int32_t *out_status);
+int ekf_landmarks_detect_dev(ekf_landmarks *h, int32_t n_scans, const float *ranges_dev, float angle_min,
+                             float angle_increment, double cluster_threshold, double *out_xyr_dev,
+                             int32_t *out_count_dev, int32_t *out_status_dev, void *cuda_stream);
 
 #ifdef __cplusplus
 }
