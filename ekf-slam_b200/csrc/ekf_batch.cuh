@@ -140,21 +140,46 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
       for (int j = 0; j <= i; ++j) pb[i][j] = pb[j][i] = S[i * (i + 1) / 2 + j];
 
     int j = -1, is_new = 0;
+    // linearisation of the landmark being fused: in the matched case it is the winning lane's own
+    // candidate evaluation, broadcast with shuffles instead of being recomputed by every lane
+    Lin L;
+    double m00 = 0.0, m01 = 0.0, m11 = 0.0, zd0 = 0.0, zd1 = 0.0;
+    bool have = false;
     if (unknown) {
       Cand best{INFINITY, 0x7fffffff};
+      // the lane's best candidate so far and what the update needs of it: the four distinct Jacobian
+      // quotients (dx/sd, dy/sd, dx/d, dy/d), S^-1 and the innovation
+      double r_xs = 0.0, r_ys = 0.0, r_xd = 0.0, r_yd = 0.0, r_m00 = 0.0, r_m01 = 0.0, r_m11 = 0.0, r_z0 = 0.0,
+             r_z1 = 0.0;
       for (int k = lane; k < cnt; k += 32) {                   // slam.cpp:361-404
         const int a = 3 + 2 * k, ra = a * (a + 1) / 2, rb = (a + 1) * (a + 2) / 2;
         const double pa[3] = {S[ra], S[ra + 1], S[ra + 2]}, pbr[3] = {S[rb], S[rb + 1], S[rb + 2]};
-        const Lin L = linearize(th, px, py, mu[a], mu[a + 1]);
+        const Lin Lk = linearize(th, px, py, mu[a], mu[a + 1]);
         const Block5 Bk = make_block5(pb, pa, pbr, S[ra + a], S[rb + a], S[rb + a + 1]);
-        const Innov I = innovation(Bk, L, p.r_noise);
-        const double zd0 = z.r - L.zhat_r, zd1 = normalize_angle(z.phi - L.zhat_b);
+        const Innov I = innovation(Bk, Lk, p.r_noise);
+        const double z0 = z.r - Lk.zhat_r, z1 = normalize_angle(z.phi - Lk.zhat_b);
         double i00, i01, i11;
-        const double d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
-        best = cand_min(best, Cand{d, k});
+        const double d = mahalanobis(I.s00, I.s01, I.s11, z0, z1, i00, i01, i11);
+        const Cand nb = cand_min(best, Cand{d, k});
+        if (nb.k == k) {
+          r_xs = Lk.h0[3]; r_ys = Lk.h0[4]; r_xd = Lk.h1[4]; r_yd = -Lk.h1[3];
+          r_m00 = i00; r_m01 = i01; r_m11 = i11; r_z0 = z0; r_z1 = z1;
+        }
+        best = nb;
       }
       best = warp_argmin(best);
-      if (best.d <= p.thr && best.k < cnt) j = best.k;         // slam.cpp:406-408,418-440
+      if (best.d <= p.thr && best.k < cnt) {                   // slam.cpp:406-408,418-440
+        j = best.k;
+        const int src = j & 31;                                // candidate k lives in lane k % 32
+        const double xs = __shfl_sync(0xffffffffu, r_xs, src), ys = __shfl_sync(0xffffffffu, r_ys, src);
+        const double xd = __shfl_sync(0xffffffffu, r_xd, src), yd = __shfl_sync(0xffffffffu, r_yd, src);
+        m00 = __shfl_sync(0xffffffffu, r_m00, src); m01 = __shfl_sync(0xffffffffu, r_m01, src);
+        m11 = __shfl_sync(0xffffffffu, r_m11, src);
+        zd0 = __shfl_sync(0xffffffffu, r_z0, src); zd1 = __shfl_sync(0xffffffffu, r_z1, src);
+        L.h0[0] = 0.0;  L.h0[1] = -xs; L.h0[2] = -ys; L.h0[3] = xs;  L.h0[4] = ys;
+        L.h1[0] = -1.0; L.h1[1] = yd;  L.h1[2] = -xd; L.h1[3] = -yd; L.h1[4] = xd;
+        have = true;
+      }
       else if (cnt < p.N) { j = cnt; is_new = 1; }
       else err = kBatchErrCapacity;
     } else {
@@ -166,7 +191,7 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
     if (lane == 0 && p.assoc_out) p.assoc_out[(size_t)f * p.m + t] = j;
     if (j < 0) continue;                                       // uniform across the warp
 
-    // ---- update with landmark j: slam.cpp:443-488 (every lane forms the same linearisation) ------
+    // ---- update with landmark j: slam.cpp:443-488 ----------------------------------------------------
     const int a = 3 + 2 * j, ra = a * (a + 1) / 2, rb = (a + 1) * (a + 2) / 2;
     double lx, ly;
     if (is_new) {                                              // slam.cpp:214-215 / :351-354
@@ -174,9 +199,8 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
       ly = py + z.r * sin(z.phi + th);
       if (unknown) cnt += 1;
     } else { lx = mu[a]; ly = mu[a + 1]; }
-    const Lin L = linearize(th, px, py, lx, ly);
-    double m00, m01, m11, zd0, zd1;
-    {
+    if (!have) {                                               // new landmark / known association
+      L = linearize(th, px, py, lx, ly);
       const double pa[3] = {S[ra], S[ra + 1], S[ra + 2]}, pbr[3] = {S[rb], S[rb + 1], S[rb + 2]};
       const Block5 Bk = make_block5(pb, pa, pbr, S[ra + a], S[rb + a], S[rb + a + 1]);
       const Innov I = innovation(Bk, L, p.r_noise);

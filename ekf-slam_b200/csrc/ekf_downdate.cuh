@@ -102,8 +102,9 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 
 // ---- chunk enumeration: strips in order, 64-row chunks inside each strip ----------------------
 struct ChunkCursor {
-  int J;      // strip
-  int row;    // first row of the chunk (global internal row index)
+  int J;          // strip
+  int row;        // first row of the chunk (global internal row index)
+  long long off;  // element offset of the chunk in the handle's Sigma storage (kept incrementally)
 };
 __device__ __forceinline__ int strip_first_row(int J, int row_begin) {
   const int r = J * EKF_STRIP;
@@ -117,20 +118,28 @@ __host__ __device__ inline long long dd_total_chunks(int chunk_rows, int row_beg
   }
   return total;
 }
-__device__ inline ChunkCursor dd_seek(long long c, int chunk_rows, int row_begin, int row_end) {
-  ChunkCursor cur{0, 0};
-  for (int J = 0; J * EKF_STRIP < row_end; ++J) {
-    const int first = strip_first_row(J, row_begin);
-    const long long here = (row_end - first) / chunk_rows;
-    if (c < here) { cur.J = J; cur.row = first + (int)c * chunk_rows; return cur; }
+__device__ inline ChunkCursor dd_seek(long long c, int chunk_rows, EkfLay lay) {
+  ChunkCursor cur{0, 0, 0};
+  for (int J = 0; J * EKF_STRIP < lay.re; ++J) {
+    const int first = ekf_lay_first_row(lay, J);
+    const long long here = (lay.re - first) / chunk_rows;
+    if (c < here) {
+      cur.J = J; cur.row = first + (int)c * chunk_rows;
+      cur.off = ekf_lay_elem(lay, cur.row, J * EKF_STRIP);
+      return cur;
+    }
     c -= here;
   }
   cur.J = -1;
   return cur;
 }
-__device__ __forceinline__ void dd_advance(ChunkCursor &cur, int chunk_rows, int row_begin, int row_end) {
+__device__ __forceinline__ void dd_advance(ChunkCursor &cur, int chunk_rows, EkfLay lay) {
   cur.row += chunk_rows;
-  if (cur.row >= row_end) { cur.J += 1; cur.row = strip_first_row(cur.J, row_begin); }
+  cur.off += (long long)chunk_rows * EKF_STRIP;          // next rows of the same strip are contiguous
+  if (cur.row >= lay.re) {
+    cur.J += 1; cur.row = ekf_lay_first_row(lay, cur.J);
+    cur.off = ekf_lay_strip_offset(lay, cur.J);
+  }
 }
 
 // Shared-memory carve-up (dynamic): [V-row stages][W strip rows][mbarriers]
@@ -188,7 +197,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
   if (warp == kComputeWarps) {
     // ================= producer warp: one elected lane feeds the V-row ring ====================
     if ((tid & 31) == 0) {
-      ChunkCursor ld = dd_seek(c_begin, CR, p.row_begin, p.row_end);
+      ChunkCursor ld = dd_seek(c_begin, CR, p.lay);
       ChunkCursor pf = ld;       // Sigma chunk to prefetch into L2: `prefetch_ahead` chunks past `ld`
       constexpr uint32_t kChunkBytes = CR * EKF_STRIP * 8;
       int pf_it = 0;
@@ -197,10 +206,10 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
         if (it >= kDdVStages) mbar_wait(&done[s], ((it / kDdVStages) - 1) & 1);
         for (; p.prefetch_ahead > 0 && pf_it <= it + p.prefetch_ahead && pf_it < n_chunks; ++pf_it) {
           if (pf_it >= 2) {      // chunks 0 and 1 are fetched by the compute warps right away
-            const double *src = p.sigma + ekf_lay_elem(p.lay, pf.row, pf.J * EKF_STRIP);
+            const double *src = p.sigma + pf.off;
             bulk_prefetch_l2(src, kChunkBytes);
           }
-          dd_advance(pf, CR, p.row_begin, p.row_end);
+          dd_advance(pf, CR, p.lay);
         }
         mbar_expect_tx(&full[s], kVBlocks * blk_bytes);
         const int vb = ld.row / EKF_PBLK;
@@ -208,7 +217,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
         for (int b = 0; b < kVBlocks; ++b)
           bulk_g2s(s_v + (s * kVBlocks + b) * blk_elems, p.V + (int64_t)(vb + b) * p.kmax * EKF_PBLK, blk_bytes,
                    &full[s]);
-        dd_advance(ld, CR, p.row_begin, p.row_end);
+        dd_advance(ld, CR, p.lay);
       }
     }
     return;
@@ -227,10 +236,10 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
   for (int i = 0; i < 4; ++i)
     toff[i] = (32 * wr + ekf_panel_row_of_slot(8 * i + g)) * EKF_STRIP + 32 * wc + 4 * t4;
 
-  ChunkCursor cur = dd_seek(c_begin, CR, p.row_begin, p.row_end);
+  ChunkCursor cur = dd_seek(c_begin, CR, p.lay);
   double c[4][4][2], cn[PF ? 4 : 1][4][2];
   if (PF) {
-    const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
+    const double *base = p.sigma + cur.off;
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -242,12 +251,12 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
   const int ksteps = k2 >> 2;
   for (int it = 0; it < n_chunks; ++it) {
     const int s = it % kDdVStages;
-    double *out = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
+    double *out = p.sigma + cur.off;
     const int curJ = cur.J;
-    dd_advance(cur, CR, p.row_begin, p.row_end);
+    dd_advance(cur, CR, p.lay);
     if (PF == 1) {
       if (it + 1 < n_chunks) {       // prefetch the next chunk's tile into the second register set
-        const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
+        const double *base = p.sigma + cur.off;
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -295,7 +304,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
       }
       ks0 = 1;
       if (it + 1 < n_chunks) {
-        const double *base = p.sigma + ekf_lay_elem(p.lay, cur.row, cur.J * EKF_STRIP);
+        const double *base = p.sigma + cur.off;
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
