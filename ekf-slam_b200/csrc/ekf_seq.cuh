@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   __shared__ Bcast s_b;
   __shared__ double s_wa[kMaxK2], s_wb[kMaxK2];
   __shared__ int s_cnt;
+  __shared__ int s_cnt0;          // counter_obstacles when the launch began
   __shared__ double s_pred[2];    // (-dy, dx)
   __shared__ double s_pb0[3][3];  // pose block right after the prediction (what Sigma_0 holds)
   __shared__ double s_zr[kMaxChunkM], s_zphi[kMaxChunkM];   // polar form of the scan's sightings
@@ -156,6 +157,7 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
   // ---------------- phase 0: pose injection, prediction, extraction of Pp / D -------------
   if (tid == 0) {
     s_cnt = *p.cnt;
+    s_cnt0 = s_cnt;
     double P[3][3];
 #pragma unroll
     for (int i = 0; i < 3; ++i)
@@ -418,7 +420,8 @@ __global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p)
     const int j = s_b.j;
     // sharded handle: which slot of the exchanged column buffer holds landmark j's raw Sigma_0 columns
     int slot = -1;
-    if (p.cols != nullptr && j >= 0 && !(unknown && s_b.is_new)) {
+    // (a landmark created during this launch has an all-zero Sigma_0 column: nothing to look up)
+    if (p.cols != nullptr && j >= 0 && !(unknown && j >= s_cnt0)) {
       slot = -2;
       if (__ldg(p.guess + t) == j) slot = t;
       else

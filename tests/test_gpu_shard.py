@@ -39,7 +39,7 @@ def _pair(N, count, shards, seed=7):
     return g, o, grid_w
 
 
-def _drive(g, o, count, grid_w, m, scans, new_in_last=0, expect_rounds=None):
+def _drive(g, o, count, grid_w, m, scans, new_in_last=0, expect_rounds=None, resight=False):
     rng = np.random.default_rng(5)
     pose = np.array([0.3, grid_w / 2.0, grid_w / 2.0])
     g.set_previous_xy(pose[1], pose[2]); o.set_prev(pose[1], pose[2])
@@ -48,6 +48,8 @@ def _drive(g, o, count, grid_w, m, scans, new_in_last=0, expect_rounds=None):
         near, xy = _scan_inputs(o.state, count, rng, m, pose)
         if s == scans - 1 and new_in_last:
             xy[:new_in_last] += 0.45
+            if resight:        # the new landmarks are sighted a second time later in the SAME scan
+                xy[m - new_in_last:] = xy[:new_in_last] + rng.normal(0, 1e-3, (new_in_last, 2))
         aG, cG, pose_after, rounds = g.scan(pose, xy)
         o.predict(*pose)
         aO = o.update_unknown(xy)
@@ -67,6 +69,14 @@ def _drive(g, o, count, grid_w, m, scans, new_in_last=0, expect_rounds=None):
 def test_sharded_map_against_oracle_b(shards):
     g, o, grid_w = _pair(300, 290, shards)
     _drive(g, o, 290, grid_w, 20, 4, new_in_last=4, expect_rounds=1)
+    g.close(); o.close()
+
+
+def test_landmark_created_and_resighted_in_one_scan_needs_no_extra_round():
+    """a landmark born in this scan has an all-zero Sigma_0 column: its second sighting in the same scan
+    is handled from the panels alone (no exchange, no stop)"""
+    g, o, grid_w = _pair(300, 290, 3)
+    _drive(g, o, 290, grid_w, 20, 2, new_in_last=3, expect_rounds=1, resight=True)
     g.close(); o.close()
 
 
