@@ -42,6 +42,9 @@
 namespace ekf {
 
 constexpr int kSeqThreads = 128;
+#ifndef EKF_SEQ_MINB
+#define EKF_SEQ_MINB 1
+#endif
 constexpr int kMaxChunkM = 24;            // measurements per sequential launch / covariance pass
 constexpr int kMaxK2 = 2 * kMaxChunkM;    // panel columns in use per pass
 
@@ -133,7 +136,7 @@ __device__ __forceinline__ double ld_plain256(const double *p, double &a, double
   return d;
 }
 
-__global__ void __launch_bounds__(kSeqThreads) ekf_seq_kernel(const SeqParams p) {
+__global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(const SeqParams p) {
   __shared__ double s_ps[3];      // pose state (theta, x, y)
   __shared__ double s_pb[3][3];   // pose block of Sigma_cur, full symmetric
   __shared__ Cand s_red[kSeqThreads / 32];
