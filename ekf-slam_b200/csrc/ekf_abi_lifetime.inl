@@ -125,6 +125,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   CKC(cudaMalloc(&f->slot_d, 2 * (size_t)f->num_sms * sizeof(double)));
   CKC(cudaMalloc(&f->slot_k, 2 * (size_t)f->num_sms * sizeof(int)));
   CKC(cudaMalloc(&f->slot_rec, 2 * (size_t)f->num_sms * kRecStride * sizeof(double)));
+  CKC(cudaFuncSetAttribute(ekf_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSeqSmemBytes));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(64, kMaxK2)));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,

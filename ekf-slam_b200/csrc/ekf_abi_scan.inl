@@ -24,7 +24,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 3 : 0;
   if (timed) CK(f, cudaEventRecord(f->ev[slot], f->stream));
   void *args[] = {(void *)&sp};
-  CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel, dim3(f->seq_grid), dim3(kSeqThreads), args, 0,
+  CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel, dim3(f->seq_grid), dim3(kSeqThreads), args, kSeqSmemBytes,
                                     f->stream));
   f->launches++;
   if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));

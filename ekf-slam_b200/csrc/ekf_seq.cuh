@@ -47,6 +47,8 @@ constexpr int kSeqThreads = 128;
 #endif
 constexpr int kMaxChunkM = 24;            // measurements per sequential launch / covariance pass
 constexpr int kMaxK2 = 2 * kMaxChunkM;    // panel columns in use per pass
+// dynamic shared memory of ekf_seq_kernel: the own-landmark V rows, [kMaxChunkM][2][kSeqThreads] double2
+constexpr size_t kSeqSmemBytes = (size_t)kMaxChunkM * 2 * kSeqThreads * sizeof(double2);
 
 // status codes latched on the device (values of ekf_status in include/ekf_slam_b200.h)
 constexpr int kErrCapacity = 2;
@@ -148,6 +150,9 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
   __shared__ double s_pred[2];    // (-dy, dx)
   __shared__ double s_pb0[3][3];  // pose block right after the prediction (what Sigma_0 holds)
   __shared__ double s_zr[kMaxChunkM], s_zphi[kMaxChunkM];   // polar form of the scan's sightings
+  // V rows (a, a+1) of the thread's FIRST landmark, [measurement][row][thread] as (column 2t, 2t+1)
+  // pairs: the deferred-downdate correction of phase D reads them back every measurement
+  extern __shared__ double2 s_vown[];
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -206,6 +211,15 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
     // barrier: every CTA reads the old values above, in no particular order
   }
   __syncthreads();
+  // The thread's first landmark (k = gtid; the only one when N <= grid threads) lives in registers for
+  // the whole launch: pose-panel rows, diagonal block, position.  Global copies are still written after
+  // every update (thread 0's serial path and the next launch read them) but never re-read by the owner.
+  double4 o_pa = make_double4(0.0, 0.0, 0.0, 0.0), o_pb = o_pa, o_dk = o_pa;
+  double2 o_lm = make_double2(0.0, 0.0);
+  if (p.side_mode && gtid < p.N) {
+    o_pa = p.Pp[4 + 2 * gtid]; o_pb = p.Pp[5 + 2 * gtid]; o_dk = p.D[gtid];
+  }
+  if (gtid < p.N) o_lm = *reinterpret_cast<const double2 *>(p.mu + 4 + 2 * gtid);
   if (!p.side_mode) {
     const double ndy = s_pred[0], pdx = s_pred[1];
     for (int k = gtid; k < p.N; k += nthreads_total) {
@@ -224,6 +238,7 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
       const double2 d0 = *reinterpret_cast<const double2 *>(dg);                // (a,a), (a,b) scratch
       const double2 d1 = *reinterpret_cast<const double2 *>(dg + EKF_STRIP);    // (b,a), (b,b)
       p.D[k] = make_double4(d0.x, d1.x, d1.y, 0.0);
+      if (k == gtid) { o_pa = va; o_pb = vb; o_dk = make_double4(d0.x, d1.x, d1.y, 0.0); }
     }
   }
 
@@ -253,9 +268,13 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
       for (int i = 0; i < kRecDoubles; ++i) rec[i] = 0.0;
       for (int k = gtid; k < cnt; k += nthreads_total) {
         const int a = 4 + 2 * k;
-        const double2 lm = *reinterpret_cast<const double2 *>(p.mu + a);
-        const double4 pa = p.Pp[a], pbr = p.Pp[a + 1];
-        const double4 dk = p.D[k];
+        double2 lm = o_lm;
+        double4 pa = o_pa, pbr = o_pb, dk = o_dk;
+        if (k != gtid) {
+          lm = *reinterpret_cast<const double2 *>(p.mu + a);
+          pa = p.Pp[a]; pbr = p.Pp[a + 1];
+          dk = p.D[k];
+        }
         const Lin L = linearize(th, px, py, lm.x, lm.y);     // slam.cpp:364-392
         const double par3[3] = {pa.x, pa.y, pa.z}, pbr3[3] = {pbr.x, pbr.y, pbr.z};
         const Block5 B = make_block5(s_pb, par3, pbr3, dk.x, dk.y, dk.z);
@@ -478,6 +497,8 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
         *reinterpret_cast<double2 *>(wp) = zero; *reinterpret_cast<double2 *>(wp + 4) = zero;
         *reinterpret_cast<double2 *>(vp) = zero; *reinterpret_cast<double2 *>(vp + 4) = zero;
       }
+      s_vown[(2 * t) * kSeqThreads + tid] = make_double2(0.0, 0.0);
+      s_vown[(2 * t + 1) * kSeqThreads + tid] = make_double2(0.0, 0.0);
     } else {
       Lin L;
       L.h0[0] = 0.0; L.h1[0] = -1.0;
@@ -518,8 +539,18 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
             const double2 c1 = __ldg(reinterpret_cast<const double2 *>(src + EKF_STRIP));
             q00 = c0.x; q10 = c0.y; q01 = c1.x; q11 = c1.y;
           }
-          // deferred downdates of earlier measurements of this scan: rows a, a+1 of V are 8
-          // contiguous doubles per k-step (this thread wrote them itself)
+          // deferred downdates of earlier measurements of this scan.  First landmark: its V rows are in
+          // shared memory; further ones: rows a, a+1 of V are 8 contiguous doubles per k-step (this
+          // thread wrote them itself).  Same accumulation order (panel column ascending) either way.
+          if (k == gtid) {
+            for (int s2 = 0; s2 < t; ++s2) {
+              const double2 va = s_vown[(2 * s2) * kSeqThreads + tid];
+              const double2 vb = s_vown[(2 * s2 + 1) * kSeqThreads + tid];
+              const double wa0 = s_wa[2 * s2], wa1 = s_wa[2 * s2 + 1], wb0 = s_wb[2 * s2], wb1 = s_wb[2 * s2 + 1];
+              q00 -= va.x * wa0; q01 -= va.x * wb0; q10 -= vb.x * wa0; q11 -= vb.x * wb0;
+              q00 -= va.y * wa1; q01 -= va.y * wb1; q10 -= vb.y * wa1; q11 -= vb.y * wb1;
+            }
+          } else {
           for (int ks = 0; ks < full_ks; ++ks) {
             double va0, va1, va2, va3, vb0, vb1, vb2, vb3;
             va3 = ld_plain256(vrow + ((int64_t)ks << 7), va0, va1, va2);
@@ -537,8 +568,11 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
             q00 -= va.x * wa[0]; q01 -= va.x * wb[0]; q10 -= vb.x * wa[0]; q11 -= vb.x * wb[0];
             q00 -= va.y * wa[1]; q01 -= va.y * wb[1]; q10 -= vb.y * wa[1]; q11 -= vb.y * wb[1];
           }
+          }
         }
-        double4 pa = p.Pp[a], pbr = p.Pp[a + 1];
+        const bool own = (k == gtid);
+        double4 pa = o_pa, pbr = o_pb;
+        if (!own) { pa = p.Pp[a]; pbr = p.Pp[a + 1]; }
         const double rowa[5] = {pa.x, pa.y, pa.z, q00, q01};
         const double rowb[5] = {pbr.x, pbr.y, pbr.z, q10, q11};
         double ga0, ga1, gb0, gb1;
@@ -546,7 +580,8 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
         row_times_ht(rowb, L, gb0, gb1);
         const double ka0 = ga0 * m00 + ga1 * m01, ka1 = ga0 * m01 + ga1 * m11;   // K = G S^-1
         const double kb0 = gb0 * m00 + gb1 * m01, kb1 = gb0 * m01 + gb1 * m11;
-        double2 lm = *reinterpret_cast<const double2 *>(p.mu + a);
+        double2 lm = o_lm;
+        if (!own) lm = *reinterpret_cast<const double2 *>(p.mu + a);
         if (k == j && s_b.is_new) { lm.x = s_b.lx; lm.y = s_b.ly; }
         lm.x = lm.x + (ka0 * zd0 + ka1 * zd1);               // slam.cpp:482
         lm.y = lm.y + (kb0 * zd0 + kb1 * zd1);
@@ -559,7 +594,8 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
         pbr.y -= kb0 * tp10 + kb1 * tp11;
         pbr.z -= kb0 * tp20 + kb1 * tp21;
         p.Pp[a] = pa; p.Pp[a + 1] = pbr;
-        double4 dk = p.D[k];
+        double4 dk = o_dk;
+        if (!own) dk = p.D[k];
         dk.x -= ka0 * ga0 + ka1 * ga1;
         dk.y -= kb0 * ga0 + kb1 * ga1;
         dk.z -= kb0 * gb0 + kb1 * gb1;
@@ -571,6 +607,11 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
         *reinterpret_cast<double2 *>(wp + 4) = make_double2(gb0, gb1);
         *reinterpret_cast<double2 *>(vp) = make_double2(ka0, ka1);
         *reinterpret_cast<double2 *>(vp + 4) = make_double2(kb0, kb1);
+        if (own) {
+          o_pa = pa; o_pb = pbr; o_dk = dk; o_lm = lm;
+          s_vown[(2 * t) * kSeqThreads + tid] = make_double2(ka0, ka1);
+          s_vown[(2 * t + 1) * kSeqThreads + tid] = make_double2(kb0, kb1);
+        }
       }
     }
     __syncthreads();  // s_b / s_wa / s_ps are rewritten by the next measurement
