@@ -122,9 +122,9 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   f->dd_ctas = env_int("EKF_DD_CTAS", 2);
   if (f->dd_ctas < 1) f->dd_ctas = 1;
   if (f->dd_prefetch < 0) f->dd_prefetch = 0;
-  CKC(cudaMalloc(&f->slot_d, 2 * (size_t)f->num_sms * sizeof(double)));
-  CKC(cudaMalloc(&f->slot_k, 2 * (size_t)f->num_sms * sizeof(int)));
-  CKC(cudaMalloc(&f->slot_rec, 2 * (size_t)f->num_sms * kRecStride * sizeof(double)));
+  CKC(cudaMalloc(&f->slot_d, (size_t)kSlotReps * 2 * f->num_sms * sizeof(double)));
+  CKC(cudaMalloc(&f->slot_k, (size_t)kSlotReps * 2 * f->num_sms * sizeof(int)));
+  CKC(cudaMalloc(&f->slot_rec, (size_t)kSlotReps * 2 * f->num_sms * kRecStride * sizeof(double)));
   CKC(cudaFuncSetAttribute(ekf_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSeqSmemBytes));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(64, kMaxK2)));

@@ -90,10 +90,15 @@ struct SeqParams {
   // grid barrier + arg-min slots
   unsigned long long *bar;
   unsigned long long bar_base;
-  double *slot_d;  // 2 * gridDim
-  int *slot_k;     // 2 * gridDim
-  double *slot_rec;  // 2 * gridDim * kRecStride: the slot candidate's update record
+  // every CTA publishes its best candidate kSlotReps times; CTA b reads replica b % kSlotReps.  A single
+  // copy made ~300 warps read the same few L2 lines right after the barrier, and the L2 slice serving
+  // a line handles those requests one after the other (3.6 us per measurement, tools/seq_phase_probe.py)
+  double *slot_d;  // [kSlotReps][2][gridDim]
+  int *slot_k;     // [kSlotReps][2][gridDim]
+  double *slot_rec;  // [kSlotReps][2][gridDim][kRecStride]: the slot candidate's update record
 };
+constexpr int kSlotReps = 8;
+constexpr int kMaxSlotsPerLane = 5;       // gridDim <= 32 * kMaxSlotsPerLane (one CTA per SM, 148 SMs)
 
 // update record of one (measurement, landmark) pair: everything the row update needs
 //   [0..3] h0[1..4]  [4..7] h1[1..4]  [8..13] T[0..2][0..1] (pose rows of G)  [14..16] S^-1
@@ -138,6 +143,18 @@ __device__ __forceinline__ double ld_plain256(const double *p, double &a, double
   return d;
 }
 
+// -DEKF_SEQ_PROF (tools/seq_phase_probe.py only): thread 0 of the first and the last CTA leave clock64()
+// stamps of the phase boundaries behind the association output, which the probe over-allocates
+#ifdef EKF_SEQ_PROF
+#define SEQ_STAMP(ph)                                                                                   \
+  do {                                                                                                  \
+    if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && p.assoc_out != nullptr)         \
+      reinterpret_cast<long long *>(p.assoc_out + 32)[((blockIdx.x != 0) * kMaxChunkM + t) * 8 + (ph)] = clock64(); \
+  } while (0)
+#else
+#define SEQ_STAMP(ph) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(const SeqParams p) {
   __shared__ double s_ps[3];      // pose state (theta, x, y)
   __shared__ double s_pb[3][3];   // pose block of Sigma_cur, full symmetric
@@ -147,6 +164,7 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
   __shared__ double s_wa[kMaxK2], s_wb[kMaxK2];
   __shared__ int s_cnt;
   __shared__ int s_cnt0;          // counter_obstacles when the launch began
+  __shared__ int s_fast;          // this measurement matched an existing landmark (decision of warp 0)
   __shared__ double s_pred[2];    // (-dy, dx)
   __shared__ double s_pb0[3][3];  // pose block right after the prediction (what Sigma_0 holds)
   __shared__ double s_zr[kMaxChunkM], s_zphi[kMaxChunkM];   // polar form of the scan's sightings
@@ -258,6 +276,7 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
     const double th = s_ps[0], px = s_ps[1], py = s_ps[2];
     const int cnt = s_cnt;
     const int par = t & 1;
+    SEQ_STAMP(0);
 
     // ---- A: Mahalanobis distance to every mapped landmark (own ones); the best candidate keeps
     //         its update record in registers --------------------------------------------------------
@@ -313,65 +332,105 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
           if (n2.k != c.k) bw = w;
           c = n2;
         }
-        double *dst = p.slot_rec + (int64_t)(par * G + blockIdx.x) * kRecStride;
-        if (lane < kRecDoubles) dst[lane] = s_wrec[bw][lane];
-        if (lane == 0) {
-          p.slot_d[par * G + blockIdx.x] = c.d;
-          p.slot_k[par * G + blockIdx.x] = c.k;
+        if (lane < kRecDoubles) {
+          const double v = s_wrec[bw][lane];
+#pragma unroll
+          for (int r = 0; r < kSlotReps; ++r)
+            p.slot_rec[(int64_t)((r * 2 + par) * G + blockIdx.x) * kRecStride + lane] = v;
+        }
+        if (lane < kSlotReps) {
+          p.slot_d[(lane * 2 + par) * G + blockIdx.x] = c.d;
+          p.slot_k[(lane * 2 + par) * G + blockIdx.x] = c.k;
         }
       }
     }
 
     // ---- B: the one grid barrier of this measurement ----------------------------------------
+    SEQ_STAMP(2);
     grid_barrier(p.bar, p.bar_base + (unsigned long long)(t + 1) * gridDim.x);
+    SEQ_STAMP(3);
 
-    // ---- C: decision (identical in every warp of every CTA) + the winner's record ------------
+    // ---- C: decision + the winner's record: warps 0 and 1 only (two requesters per CTA on the slot
+    //         lines), broadcast to the rest of the CTA through shared memory ----------------------------
     bool fast = false;   // matched an existing landmark: record comes from the winner's slot
     int jfast = -1;
     if (unknown) {
-      Cand c{INFINITY, 0x7fffffff};
-      int bstar = 0;
-      for (int b = lane; b < G; b += 32) {
-        const Cand o{ldcg_d(p.slot_d + par * G + b), __ldcg(p.slot_k + par * G + b)};
-        const Cand n2 = cand_min(c, o);
-        if (n2.k != c.k) bstar = b;
-        c = n2;
-      }
+      if (warp < 2) {
+        const int rep = (int)(blockIdx.x % kSlotReps);
+        const double *sd = p.slot_d + (rep * 2 + par) * G;
+        const int *sk = p.slot_k + (rep * 2 + par) * G;
+        double od[kMaxSlotsPerLane];
+        int ok[kMaxSlotsPerLane];
 #pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        Cand o;
-        o.d = __shfl_xor_sync(0xffffffffu, c.d, off);
-        o.k = __shfl_xor_sync(0xffffffffu, c.k, off);
-        const int ob = __shfl_xor_sync(0xffffffffu, bstar, off);
-        const Cand n2 = cand_min(c, o);
-        if (n2.k != c.k) bstar = ob;
-        c = n2;
-      }
-      // the tentative landmark sits last with distance == threshold and wins only on a
-      // strictly smaller value: slam.cpp:406-408,418-440
-      fast = (c.d <= p.thr && c.k < cnt);
-      if (fast) {
-        jfast = c.k;
-        if (warp == 0) {
-          if (lane < kRecDoubles)
-            s_b.rec[lane] = ldcg_d(p.slot_rec + (int64_t)(par * G + bstar) * kRecStride + lane);
-          if (lane == 0) {
-            s_b.j = jfast; s_b.is_new = 0;
-            if (blockIdx.x == 0 && p.assoc_out) p.assoc_out[t] = jfast;
+        for (int i = 0; i < kMaxSlotsPerLane; ++i) {     // all loads in flight together
+          const int b = lane + 32 * i;
+          od[i] = INFINITY; ok[i] = 0x7fffffff;
+          if (b < G) { od[i] = ldcg_d(sd + b); ok[i] = __ldcg(sk + b); }
+        }
+        Cand c{INFINITY, 0x7fffffff};
+        int bstar = 0;
+#ifdef EKF_SEQ_PROF
+        if (od[0] + od[1] + od[2] + od[3] + od[4] == -1.0) bstar = 1;   // wait for the loads
+        SEQ_STAMP(1);
+#endif
+#pragma unroll
+        for (int i = 0; i < kMaxSlotsPerLane; ++i) {
+          const int b = lane + 32 * i;
+          if (b < G) {
+            const Cand o{od[i], ok[i]};
+            const Cand n2 = cand_min(c, o);
+            if (n2.k != c.k) bstar = b;
+            c = n2;
           }
-        } else if (warp == 1 || kSeqThreads == 32) {
-          // panel history of the chosen landmark's two rows (column operand of the correction)
-          const int a = 4 + 2 * jfast;
-          const double *wrow = p.W + (((int64_t)(a >> 5) * nks) << 7) + (ekf_panel_slot(a & 31) << 2);
-          for (int i = lane; i < 8 * ((t + 1) >> 1); i += 32) {   // 8 doubles per k-step, q < 2t
-            const int ks = i >> 3, w = i & 7, q = 4 * ks + (w & 3);
-            if (q < 2 * t) {
-              const double v = ldcg_d(wrow + ((int64_t)ks << 7) + w);
-              if (w < 4) s_wa[q] = v; else s_wb[q] = v;
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          Cand o;
+          o.d = __shfl_xor_sync(0xffffffffu, c.d, off);
+          o.k = __shfl_xor_sync(0xffffffffu, c.k, off);
+          const int ob = __shfl_xor_sync(0xffffffffu, bstar, off);
+          const Cand n2 = cand_min(c, o);
+          if (n2.k != c.k) bstar = ob;
+          c = n2;
+        }
+        SEQ_STAMP(7);
+        // the tentative landmark sits last with distance == threshold and wins only on a
+        // strictly smaller value: slam.cpp:406-408,418-440
+        fast = (c.d <= p.thr && c.k < cnt);
+        if (tid == 0) s_fast = fast ? 1 : 0;
+        if (fast) {
+          jfast = c.k;
+          if (warp == 0) {
+            if (lane < kRecDoubles)
+              s_b.rec[lane] = ldcg_d(p.slot_rec + (int64_t)((rep * 2 + par) * G + bstar) * kRecStride + lane);
+            if (lane == 0) {
+              s_b.j = jfast; s_b.is_new = 0;
+              if (blockIdx.x == 0 && p.assoc_out) p.assoc_out[t] = jfast;
+            }
+          } else {
+            // panel history of the chosen landmark's two rows (column operand of the correction):
+            // 8 doubles per k-step, columns q < 2t; at most 3 per lane, all in flight together
+            const int a = 4 + 2 * jfast;
+            const double *wrow = p.W + (((int64_t)(a >> 5) * nks) << 7) + (ekf_panel_slot(a & 31) << 2);
+            double wv[3];
+#pragma unroll
+            for (int u = 0; u < 3; ++u) {
+              const int i = lane + 32 * u;
+              const int ks = i >> 3, w = i & 7, q = 4 * ks + (w & 3);
+              wv[u] = 0.0;
+              if (q < 2 * t) wv[u] = ldcg_d(wrow + ((int64_t)ks << 7) + w);
+            }
+#pragma unroll
+            for (int u = 0; u < 3; ++u) {
+              const int i = lane + 32 * u;
+              const int ks = i >> 3, w = i & 7, q = 4 * ks + (w & 3);
+              if (q < 2 * t) { if (w < 4) s_wa[q] = wv[u]; else s_wb[q] = wv[u]; }
             }
           }
         }
       }
+      __syncthreads();
+      fast = s_fast != 0;
     }
     if (!fast) {
       // serial path (thread 0): new landmark, known association, skipped sighting, errors
@@ -437,8 +496,9 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
           }
         }
       }
+      __syncthreads();
     }
-    __syncthreads();
+    SEQ_STAMP(4);
     const int j = s_b.j;
     // sharded handle: which slot of the exchanged column buffer holds landmark j's raw Sigma_0 columns
     int slot = -1;
@@ -614,7 +674,9 @@ __global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(cons
         }
       }
     }
+    SEQ_STAMP(5);
     __syncthreads();  // s_b / s_wa / s_ps are rewritten by the next measurement
+    SEQ_STAMP(6);
   }
 
   // columns [2 * done, round-up-to-4(2m)) of both panels are zeroed: the covariance pass works on whole
