@@ -61,6 +61,7 @@ struct ekf_filter {
   int64_t ev_count = 0;    // scans recorded since timing was enabled
   int64_t launches = 0;
   int seq_grid = 1;
+  int seq_threads = 64;    // shape of the sequential kernel (ekf_seq.cuh)
   int dd_grid = 1;
   int dd_prefetch = 0;
   int dd_ctas = 2;

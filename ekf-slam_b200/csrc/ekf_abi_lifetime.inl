@@ -109,11 +109,29 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   CKC(cudaMalloc(&f->prev_xy, 2 * sizeof(double)));
   CKC(cudaMalloc(&f->bar, sizeof(unsigned long long)));
 
-  // grids: sequential kernel = cooperative, at most one CTA per SM; covariance pass = one CTA per SM
-  int seq_blocks = (f->N + kSeqThreads - 1) / kSeqThreads;
-  int max_seq = env_int("EKF_SEQ_BLOCKS", f->num_sms);
+  // grids: sequential kernel = cooperative (shape chosen from N, see ekf_seq.cuh); covariance pass = one CTA per SM
+  CKC(cudaFuncSetAttribute(ekf_seq_kernel<kSeqThreadsSmall>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)seq_smem_bytes(kSeqThreadsSmall)));
+  CKC(cudaFuncSetAttribute(ekf_seq_kernel<kSeqThreadsLarge>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)seq_smem_bytes(kSeqThreadsLarge)));
+  // co-resident CTAs the cooperative launch may use (occupancy of the kernel with its dynamic smem), capped by
+  // what one warp can scan in the arg-min slot read
+  int seq_occ = 1;
+  CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&seq_occ, ekf_seq_kernel<kSeqThreadsSmall>, kSeqThreadsSmall,
+                                                    seq_smem_bytes(kSeqThreadsSmall)));
+  if (seq_occ < 1) seq_occ = 1;
+  if (seq_occ > kSeqCtasPerSm) seq_occ = kSeqCtasPerSm;
+  int seq_cap = f->num_sms * seq_occ;
+  if (seq_cap > 32 * kMaxSlotsPerLane) seq_cap = 32 * kMaxSlotsPerLane;
+  f->seq_threads = env_int("EKF_SEQ_THREADS", f->N <= seq_cap * kSeqThreadsSmall ? kSeqThreadsSmall : kSeqThreadsLarge);
+  if (f->seq_threads != kSeqThreadsSmall) {
+    f->seq_threads = kSeqThreadsLarge;
+    if (seq_cap > f->num_sms) seq_cap = f->num_sms;      // one CTA per SM
+  }
+  int seq_blocks = (f->N + f->seq_threads - 1) / f->seq_threads;
+  int max_seq = env_int("EKF_SEQ_BLOCKS", seq_cap);
   if (max_seq < 1) max_seq = 1;
-  if (max_seq > f->num_sms) max_seq = f->num_sms;
+  if (max_seq > seq_cap) max_seq = seq_cap;
   f->seq_grid = seq_blocks < max_seq ? seq_blocks : max_seq;
   f->dd_grid = env_int("EKF_DD_BLOCKS", f->num_sms);
   if (f->dd_grid < 1) f->dd_grid = 1;
@@ -122,10 +140,9 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   f->dd_ctas = env_int("EKF_DD_CTAS", 2);
   if (f->dd_ctas < 1) f->dd_ctas = 1;
   if (f->dd_prefetch < 0) f->dd_prefetch = 0;
-  CKC(cudaMalloc(&f->slot_d, (size_t)kSlotReps * 2 * f->num_sms * sizeof(double)));
-  CKC(cudaMalloc(&f->slot_k, (size_t)kSlotReps * 2 * f->num_sms * sizeof(int)));
-  CKC(cudaMalloc(&f->slot_rec, (size_t)kSlotReps * 2 * f->num_sms * kRecStride * sizeof(double)));
-  CKC(cudaFuncSetAttribute(ekf_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSeqSmemBytes));
+  CKC(cudaMalloc(&f->slot_d, (size_t)kSlotReps * 2 * seq_cap * sizeof(double)));
+  CKC(cudaMalloc(&f->slot_k, (size_t)kSlotReps * 2 * seq_cap * sizeof(int)));
+  CKC(cudaMalloc(&f->slot_rec, (size_t)kSlotReps * 2 * seq_cap * kRecStride * sizeof(double)));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(64, kMaxK2)));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -24,8 +24,10 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 3 : 0;
   if (timed) CK(f, cudaEventRecord(f->ev[slot], f->stream));
   void *args[] = {(void *)&sp};
-  CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel, dim3(f->seq_grid), dim3(kSeqThreads), args, kSeqSmemBytes,
-                                    f->stream));
+  const void *seq_fn = f->seq_threads == kSeqThreadsSmall ? (const void *)ekf_seq_kernel<kSeqThreadsSmall>
+                                                          : (const void *)ekf_seq_kernel<kSeqThreadsLarge>;
+  CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
+                                    seq_smem_bytes(f->seq_threads), f->stream));
   f->launches++;
   if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
   if (mc > 0) {

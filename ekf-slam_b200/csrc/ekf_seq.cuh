@@ -41,14 +41,19 @@
 
 namespace ekf {
 
-constexpr int kSeqThreads = 128;
+// Two shapes of the sequential kernel (template parameter NT = threads per CTA), chosen per handle:
+//   NT =  64, up to 2 CTAs / SM: every thread owns ONE landmark while N <= 160 * 64; the phase is a chain
+//            of latencies, and small CTAs keep the CTA-level reductions and barriers short
+//   NT = 256, 1 CTA / SM: larger maps, where a thread owns several landmarks and throughput matters
+constexpr int kSeqThreadsSmall = 64, kSeqThreadsLarge = 256;
+constexpr int kSeqCtasPerSm = 2;          // cooperative grid: at most this many CTAs per SM (NT = 64)
 #ifndef EKF_SEQ_MINB
 #define EKF_SEQ_MINB 1
 #endif
 constexpr int kMaxChunkM = 24;            // measurements per sequential launch / covariance pass
 constexpr int kMaxK2 = 2 * kMaxChunkM;    // panel columns in use per pass
-// dynamic shared memory of ekf_seq_kernel: the own-landmark V rows, [kMaxChunkM][2][kSeqThreads] double2
-constexpr size_t kSeqSmemBytes = (size_t)kMaxChunkM * 2 * kSeqThreads * sizeof(double2);
+// dynamic shared memory of ekf_seq_kernel: the own-landmark V rows, [kMaxChunkM][2][NT] double2
+constexpr size_t seq_smem_bytes(int nt) { return (size_t)kMaxChunkM * 2 * nt * sizeof(double2); }
 
 // status codes latched on the device (values of ekf_status in include/ekf_slam_b200.h)
 constexpr int kErrCapacity = 2;
@@ -155,7 +160,9 @@ __device__ __forceinline__ double ld_plain256(const double *p, double &a, double
 #define SEQ_STAMP(ph) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(kSeqThreads, EKF_SEQ_MINB) ekf_seq_kernel(const SeqParams p) {
+template <int NT>
+__global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqParams p) {
+  constexpr int kSeqThreads = NT;
   __shared__ double s_ps[3];      // pose state (theta, x, y)
   __shared__ double s_pb[3][3];   // pose block of Sigma_cur, full symmetric
   __shared__ Cand s_red[kSeqThreads / 32];

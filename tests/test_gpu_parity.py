@@ -190,6 +190,17 @@ def test_procedural_map_against_oracle_b(N, count, m, scans):
     g.close(); o.close()
 
 
+@pytest.mark.parametrize("threads,blocks", [(256, None), (64, 3), (256, 1)])
+def test_sequential_kernel_shapes(threads, blocks, monkeypatch):
+    """both shapes of the sequential kernel (ekf_seq.cuh: 64 threads x up to 2 CTAs / SM for maps of one
+    landmark per thread, 256 x 1 for larger ones), and grids so small that a thread owns several landmarks
+    (first one cached in registers / shared memory, the others through global memory)"""
+    monkeypatch.setenv("EKF_SEQ_THREADS", str(threads))
+    if blocks is not None:
+        monkeypatch.setenv("EKF_SEQ_BLOCKS", str(blocks))
+    test_procedural_map_against_oracle_b(1000, 990, 20, 3)
+
+
 def test_full_size_N10k_one_scan_against_oracle_b():
     """BASELINE config 4 at full size (N = 10,000, n = 20,003, m = 20): one whole scan against
     oracle B seeded with the GPU's own procedural map; plus size-independent properties."""
