@@ -34,6 +34,9 @@ struct ekf_filter {
   double *cols = nullptr;  // sharded: exchange buffer, kMaxChunkM x n_pad x 2
   int *guess = nullptr;    // sharded: speculative association of the round
   int *done_dev = nullptr; // sharded: measurements processed by the last finish
+  double *guess_part_d = nullptr;        // sharded: per-slice partial candidates of the speculative association
+  int *guess_part_k = nullptr;
+  unsigned int *guess_ticket = nullptr;
   // the round opened by ekf_shard_scan_begin
   int pend_m = -1, pend_finish = 0;
   const double *pend_xy = nullptr;

@@ -9,6 +9,12 @@ int shard_buffers(ekf_filter *f) {
   if (!f->cols) CK(f, cudaMalloc(&f->cols, (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double)));
   if (!f->guess) CK(f, cudaMalloc(&f->guess, kMaxChunkM * sizeof(int)));
   if (!f->done_dev) CK(f, cudaMalloc(&f->done_dev, sizeof(int)));
+  if (!f->guess_part_d) {
+    CK(f, cudaMalloc(&f->guess_part_d, (size_t)kMaxChunkM * kGuessMaxSlices * sizeof(double)));
+    CK(f, cudaMalloc(&f->guess_part_k, (size_t)kMaxChunkM * kGuessMaxSlices * sizeof(int)));
+    CK(f, cudaMalloc(&f->guess_ticket, kMaxChunkM * sizeof(unsigned int)));
+    CK(f, cudaMemsetAsync(f->guess_ticket, 0, kMaxChunkM * sizeof(unsigned int), f->stream));
+  }
   return EKF_OK;
 }
 
@@ -58,8 +64,14 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
                                                             f->cfg.q_noise);
     f->launches++;
   }
-  shard_guess_kernel<<<mc, kGuessThreads, 0, f->stream>>>(f->Pp, f->D, f->mu, f->cnt, xy_dev, ids_dev, f->guess,
-                                                          f->cfg.r_noise, f->cfg.mah_threshold);
+  int slices = (2 * f->num_sms + mc - 1) / mc;        // about two CTAs per SM in total
+  const int useful = (f->N + kGuessThreads - 1) / kGuessThreads;
+  if (slices > useful) slices = useful;
+  if (slices > kGuessMaxSlices) slices = kGuessMaxSlices;
+  if (slices < 1) slices = 1;
+  shard_guess_kernel<<<dim3(mc, slices), kGuessThreads, 0, f->stream>>>(
+      f->Pp, f->D, f->mu, f->cnt, xy_dev, ids_dev, f->guess, f->cfg.r_noise, f->cfg.mah_threshold, f->guess_part_d,
+      f->guess_part_k, f->guess_ticket);
   // test-only fault injection: forget the speculation for one sighting so that the stop / resume path runs
   const int drop = env_int("EKF_SHARD_DROP_GUESS", -1);
   if (drop >= 0 && drop < mc) CK(f, cudaMemsetAsync(f->guess + drop, 0xFF, sizeof(int), f->stream));
@@ -114,10 +126,10 @@ int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, 
   dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;
   dp.lay = f->lay; dp.row_begin = f->lay.rb; dp.row_end = f->lay.re;
   dp.prefetch_ahead = f->dd_prefetch;
-  dp.total_chunks = dd_total_chunks(32, dp.row_begin, dp.row_end);
-  long long grid = (long long)f->dd_grid * f->dd_ctas;
+  dp.total_chunks = dd_total_chunks(64, dp.row_begin, dp.row_end);   // shard bounds are multiples of 128 rows
+  long long grid = f->dd_grid;
   if (grid > dp.total_chunks) grid = dp.total_chunks;
-  ekf_downdate_kernel<32, 0><<<(unsigned)grid, dd_threads(32), dd_smem_bytes(32, dp.k2), f->stream>>>(dp);
+  ekf_downdate_kernel<64, 2><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
   shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
   f->launches += 2;
   CK(f, cudaGetLastError());

@@ -78,16 +78,21 @@ __global__ void shard_predict_kernel(double4 *Pp, double *mu, const double *pose
   }
 }
 
-// ---- speculative association: one CTA per sighting, against the scan-start state ------------------
+// ---- speculative association against the scan-start state: grid (m sightings, P slices of the map) ----
+// every CTA reduces its slice to one candidate; the last CTA of a sighting to finish (ticket counter)
+// reduces the P partial candidates and writes guess[t].  m * P is sized to about two CTAs per SM.
 constexpr int kGuessThreads = 256;
+constexpr int kGuessMaxSlices = 32;
 __global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double4 *Pp, const double4 *D,
                                                                    const double *mu, const int *cnt_p,
                                                                    const double *xy, const int *ids, int *guess,
-                                                                   double r_noise, double thr) {
+                                                                   double r_noise, double thr, double *part_d,
+                                                                   int *part_k, unsigned int *ticket) {
   __shared__ Cand s_red[kGuessThreads / 32];
-  const int t = blockIdx.x;
+  __shared__ int s_last;
+  const int t = blockIdx.x, slice = blockIdx.y, P = gridDim.y;
   if (ids != nullptr) {                                    // known association: nothing to speculate
-    if (threadIdx.x == 0) guess[t] = ids[t];
+    if (threadIdx.x == 0 && slice == 0) guess[t] = ids[t];
     return;
   }
   const int cnt = *cnt_p;
@@ -100,7 +105,7 @@ __global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double
     pb[i][0] = r.x; pb[i][1] = r.y; pb[i][2] = r.z;
   }
   Cand best{INFINITY, 0x7fffffff};
-  for (int k = threadIdx.x; k < cnt; k += kGuessThreads) {
+  for (int k = slice * kGuessThreads + threadIdx.x; k < cnt; k += P * kGuessThreads) {
     const int a = 4 + 2 * k;
     const double2 lm = *reinterpret_cast<const double2 *>(mu + a);
     const double4 pa = Pp[a], pbr = Pp[a + 1], dk = D[k];
@@ -119,9 +124,21 @@ __global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double
   if (threadIdx.x == 0) {
     Cand c = s_red[0];
     for (int w = 1; w < kGuessThreads / 32; ++w) c = cand_min(c, s_red[w]);
-    // generous acceptance (4 x threshold): a sighting that is borderline now may match after the
-    // earlier updates of the scan; an unnecessary column costs nothing but bandwidth
-    guess[t] = (c.k < cnt && c.d <= 4.0 * thr) ? c.k : -1;
+    part_d[t * kGuessMaxSlices + slice] = c.d;
+    part_k[t * kGuessMaxSlices + slice] = c.k;
+    __threadfence();
+    const unsigned int prev = atomicAdd(ticket + t, 1u);
+    s_last = (prev == (unsigned int)(P - 1));
+    if (s_last) {
+      __threadfence();
+      ticket[t] = 0;                                       // ready for the next launch
+      Cand g{INFINITY, 0x7fffffff};
+      for (int q = 0; q < P; ++q)
+        g = cand_min(g, Cand{__ldcg(part_d + t * kGuessMaxSlices + q), __ldcg(part_k + t * kGuessMaxSlices + q)});
+      // generous acceptance (4 x threshold): a sighting that is borderline now may match after the
+      // earlier updates of the scan; an unnecessary column costs nothing but bandwidth
+      guess[t] = (g.k < cnt && g.d <= 4.0 * thr) ? g.k : -1;
+    }
   }
 }
 
