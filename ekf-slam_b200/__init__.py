@@ -100,6 +100,13 @@ def load() -> C.CDLL:
         "ekf_landmarks_destroy": (C.c_int, [vp]),
         "ekf_landmarks_detect": (C.c_int, [vp, i32, C.POINTER(C.c_float), C.c_float, C.c_float, C.c_double, dp, ip, ip]),
         "ekf_landmarks_detect_dev": (C.c_int, [vp, i32, vp, C.c_float, C.c_float, C.c_double, vp, vp, vp, vp]),
+        "ekf_nusim_create": (C.c_int, [i32, dp, C.c_double, C.c_double, i32, C.POINTER(vp)]),
+        "ekf_nusim_destroy": (C.c_int, [vp]),
+        "ekf_nusim_wall_lines": (C.c_int, [vp, dp]),
+        "ekf_nusim_fake_sensor": (C.c_int, [vp, i32, dp, C.c_double, C.c_double, C.c_uint64, dp, dp, ip]),
+        "ekf_nusim_fake_sensor_dev": (C.c_int, [vp, i32, vp, C.c_double, C.c_double, C.c_uint64, vp, vp, vp, vp]),
+        "ekf_nusim_lidar": (C.c_int, [vp, i32, dp, C.c_double, C.c_double, C.c_uint64, dp, C.POINTER(C.c_float)]),
+        "ekf_nusim_lidar_dev": (C.c_int, [vp, i32, vp, C.c_double, C.c_double, C.c_uint64, vp, vp, vp]),
         "ekf_batch_create": (C.c_int, [C.POINTER(EkfConfig), i32, C.POINTER(vp)]),
         "ekf_batch_destroy": (C.c_int, [vp]),
         "ekf_batch_set_stream": (C.c_int, [vp, vp]),
@@ -505,3 +512,72 @@ class LandmarkExtractor:
         if rc != EKF_OK:
             raise EkfError(rc, "ekf_landmarks_detect")
         return [out[s, :min(int(cnt[s]), self.max_out)].copy() for s in range(ns)], st
+
+
+class NuSim:
+    """nusim's sensor models on the device for many robots at once (ekf_nusim_*): the fake landmark sensor
+    (nusim/src/nusim.cpp:310-349) and the 360-beam lidar (nusim.cpp:559-710)."""
+
+    def __init__(self, obstacles_xyr, arena_x: float, arena_y: float, device: int = -1):
+        self._L = load()
+        obs = np.ascontiguousarray(obstacles_xyr, dtype=np.float64).reshape(-1, 3)
+        h = C.c_void_p()
+        rc = self._L.ekf_nusim_create(obs.shape[0], _dp(obs), arena_x, arena_y, device, C.byref(h))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_nusim_create")
+        self._h, self.n_obstacles = h, obs.shape[0]
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ekf_nusim_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def wall_lines(self):
+        out = np.zeros((4, 4))
+        rc = self._L.ekf_nusim_wall_lines(self._h, _dp(out))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_nusim_wall_lines")
+        return out
+
+    def fake_sensor(self, poses, max_range: float, noise_std: float = 0.0, seed: int = 0, noise=None):
+        """poses [n, 3] (theta, x, y) -> (xy [n, n_obstacles, 2], ids [n, n_obstacles])"""
+        poses = np.ascontiguousarray(poses, dtype=np.float64).reshape(-1, 3)
+        n = poses.shape[0]
+        xy = np.zeros((n, self.n_obstacles, 2))
+        ids = np.zeros((n, self.n_obstacles), dtype=np.int32)
+        nz = None if noise is None else np.ascontiguousarray(noise, dtype=np.float64).reshape(n, self.n_obstacles, 2)
+        rc = self._L.ekf_nusim_fake_sensor(self._h, n, _dp(poses), max_range, noise_std, seed,
+                                           None if nz is None else _dp(nz), _dp(xy), _ip(ids))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_nusim_fake_sensor")
+        return xy, ids
+
+    def lidar(self, poses, max_range: float, noise_std: float = 0.0, seed: int = 0, noise=None):
+        """poses [n, 3] (theta, x, y) -> ranges [n, 360] float32"""
+        poses = np.ascontiguousarray(poses, dtype=np.float64).reshape(-1, 3)
+        n = poses.shape[0]
+        out = np.zeros((n, 360), dtype=np.float32)
+        nz = None if noise is None else np.ascontiguousarray(noise, dtype=np.float64).reshape(n, 360)
+        rc = self._L.ekf_nusim_lidar(self._h, n, _dp(poses), max_range, noise_std, seed,
+                                     None if nz is None else _dp(nz), out.ctypes.data_as(C.POINTER(C.c_float)))
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_nusim_lidar")
+        return out
+
+    def fake_sensor_dev(self, n, poses_ptr, max_range, noise_std, seed, xy_ptr, ids_ptr, stream=0, noise_ptr=0):
+        rc = self._L.ekf_nusim_fake_sensor_dev(self._h, n, poses_ptr, max_range, noise_std, seed, noise_ptr or None,
+                                               xy_ptr, ids_ptr, stream or None)
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_nusim_fake_sensor_dev")
+
+    def lidar_dev(self, n, poses_ptr, max_range, noise_std, seed, ranges_ptr, stream=0, noise_ptr=0):
+        rc = self._L.ekf_nusim_lidar_dev(self._h, n, poses_ptr, max_range, noise_std, seed, noise_ptr or None,
+                                         ranges_ptr, stream or None)
+        if rc != EKF_OK:
+            raise EkfError(rc, "ekf_nusim_lidar_dev")

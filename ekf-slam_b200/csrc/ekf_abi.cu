@@ -16,6 +16,7 @@
 #include "ekf_downdate.cuh"
 #include "ekf_landmarks.cuh"
 #include "ekf_layout.h"
+#include "ekf_nusim.cuh"
 #include "ekf_seq.cuh"
 #include "ekf_shard.cuh"
 #include "ekf_util.cuh"
@@ -163,3 +164,4 @@ int env_int(const char *name, int dflt) {
 #include "ekf_abi_batch.inl"
 #include "ekf_abi_shard.inl"
 #include "ekf_abi_landmarks.inl"
+#include "ekf_abi_nusim.inl"

@@ -64,6 +64,7 @@ typedef struct ekf_config {
 typedef struct ekf_filter ekf_filter;       /* one EKF (slam.cpp:659-676) */
 typedef struct ekf_batch ekf_batch;         /* B independent small EKFs, one CTA each */
 typedef struct ekf_landmarks ekf_landmarks; /* landmark extraction from LaserScans (the EKF's producer) */
+typedef struct ekf_nusim ekf_nusim;         /* nusim's sensor models as device-side generators */
 
 void ekf_default_config(ekf_config *cfg);
 const char *ekf_status_string(int status);
@@ -221,6 +222,34 @@ int ekf_landmarks_detect(ekf_landmarks *h, int32_t n_scans, const float *ranges,
 int ekf_landmarks_detect_dev(ekf_landmarks *h, int32_t n_scans, const float *ranges_dev, float angle_min,
                              float angle_increment, double cluster_threshold, double *out_xyr_dev,
                              int32_t *out_count_dev, int32_t *out_status_dev, void *cuda_stream);
+
+/* ---- nusim's sensor models on the device ---------------------------------------
+ * The world of nusim/config/basic_world.yaml: n_obstacles cylinders (x, y, r) and a rectangular arena;
+ * n_robots poses (theta, x, y) in the world frame at once (the Monte-Carlo replicas).
+ *   fake sensor (nusim/src/nusim.cpp:310-349): out_xy[robot][obstacle][2] = the obstacle in the robot's
+ *     body frame + noise per axis; out_ids[robot][obstacle] = obstacle index when its TRUE range is
+ *     <= max_range (Marker::ADD), else -(index + 1) (Marker::DELETE) - the layout and the negative-id
+ *     rule ekf_batch_step takes for known association.
+ *   lidar (nusim.cpp:559-710): out_ranges[robot][360] float, beam i at i degrees from the scanner at
+ *     (-0.032, 0) in the body frame; cylinders first, the arena's wall lines only when no cylinder was
+ *     hit; clamped to [0.11, 10]; + noise.  Feeds ekf_landmarks_detect with angle_min 0, increment 2pi/360.
+ * Noise: `noise` (same shape as the output, doubles) holds the caller's draws where the reference adds
+ * sensor_normal_dist(gen); with noise == NULL and noise_std > 0 a counter-based N(0, noise_std) generator
+ * keyed by (seed, robot, index) is used (nusim.cpp:202 passes the "variance" parameter as the stddev). */
+int ekf_nusim_create(int32_t n_obstacles, const double *obstacles_xyr, double arena_x_length, double arena_y_length,
+                     int32_t device, ekf_nusim **out);
+int ekf_nusim_destroy(ekf_nusim *h);
+/* the two points (x3, y3, x4, y4) per wall of the lines the lidar intersects (nusim.cpp:649-653): 16 doubles */
+int ekf_nusim_wall_lines(ekf_nusim *h, double *out16);
+int ekf_nusim_fake_sensor(ekf_nusim *h, int32_t n_robots, const double *poses, double max_range, double noise_std,
+                          uint64_t seed, const double *noise, double *out_xy, int32_t *out_ids);
+int ekf_nusim_fake_sensor_dev(ekf_nusim *h, int32_t n_robots, const double *poses_dev, double max_range,
+                              double noise_std, uint64_t seed, const double *noise_dev, double *out_xy_dev,
+                              int32_t *out_ids_dev, void *cuda_stream);
+int ekf_nusim_lidar(ekf_nusim *h, int32_t n_robots, const double *poses, double max_range, double noise_std,
+                    uint64_t seed, const double *noise, float *out_ranges);
+int ekf_nusim_lidar_dev(ekf_nusim *h, int32_t n_robots, const double *poses_dev, double max_range, double noise_std,
+                        uint64_t seed, const double *noise_dev, float *out_ranges_dev, void *cuda_stream);
 
 #ifdef __cplusplus
 }
