@@ -6,6 +6,7 @@ struct ekf_batch {
   int B = 0, N = 0, n = 0, tri = 0;
   double *sigma = nullptr, *mu = nullptr, *prev = nullptr;
   int *cnt = nullptr, *status = nullptr;
+  uchar2 *tri_map = nullptr;     // (row, column) of every packed lower-triangle element
   // staging for the host-pointer step
   unsigned char *io_dev = nullptr, *io_host = nullptr, *res_dev = nullptr, *res_host = nullptr;
   size_t io_cap = 0, res_cap = 0;
@@ -32,6 +33,7 @@ int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, con
   p.B = b->B; p.N = b->N; p.n = b->n; p.tri = b->tri;
   p.q_noise = b->cfg.q_noise; p.r_noise = b->cfg.r_noise; p.thr = b->cfg.mah_threshold;
   p.sigma = b->sigma; p.mu = b->mu; p.prev = b->prev; p.cnt = b->cnt; p.status = b->status;
+  p.tri_map = b->tri_map;
   p.pose = poses; p.xy = xy; p.ids = ids; p.m_count = m_count; p.m = m;
   p.assoc_out = assoc; p.cnt_out = count; p.pose_out = pose_out;
   if (batch_smem_bytes(b->n, m) > 200 * 1024) return EKF_ERR_INVALID;   // m beyond the per-CTA shared memory
@@ -82,7 +84,7 @@ int ekf_batch_destroy(ekf_batch *b) {
   {
     DeviceGuard guard(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
-    cudaFree(b->sigma); cudaFree(b->mu); cudaFree(b->prev); cudaFree(b->cnt); cudaFree(b->status);
+    cudaFree(b->sigma); cudaFree(b->mu); cudaFree(b->prev); cudaFree(b->cnt); cudaFree(b->status); cudaFree(b->tri_map);
     cudaFree(b->io_dev); cudaFree(b->res_dev);
     if (b->io_host) cudaFreeHost(b->io_host);
     if (b->res_host) cudaFreeHost(b->res_host);
@@ -122,6 +124,14 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
   CKC(cudaMalloc(&b->prev, (size_t)b->B * 2 * sizeof(double)));
   CKC(cudaMalloc(&b->cnt, (size_t)b->B * sizeof(int)));
   CKC(cudaMalloc(&b->status, sizeof(int)));
+  {
+    std::vector<uchar2> map((size_t)b->tri);
+    size_t e = 0;
+    for (int i = 0; i < b->n; ++i)
+      for (int c = 0; c <= i; ++c) map[e++] = make_uchar2((unsigned char)i, (unsigned char)c);
+    CKC(cudaMalloc(&b->tri_map, (size_t)b->tri * sizeof(uchar2)));
+    CKC(cudaMemcpy(b->tri_map, map.data(), (size_t)b->tri * sizeof(uchar2), cudaMemcpyHostToDevice));
+  }
   CKC(cudaMemsetAsync(b->sigma, 0, sig_bytes, b->stream));
   CKC(cudaMemsetAsync(b->mu, 0, (size_t)b->B * b->n * sizeof(double), b->stream));
   CKC(cudaMemsetAsync(b->prev, 0, (size_t)b->B * 2 * sizeof(double), b->stream));

@@ -29,6 +29,7 @@ struct BatchParams {
   double *sigma, *mu, *prev;
   int *cnt;
   int *status;             // latched error (max over filters)
+  const uchar2 *tri_map;   // [tri] (row, column) of packed lower-triangle element e (n <= 131 < 256)
   // this step (device pointers)
   const double *pose;      // [B][3] (theta, x, y) composed odometry pose
   const double *xy;        // [B][m][2]
@@ -223,18 +224,13 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
       mu[i] = v;
     }
     __syncwarp();
-    // Sigma -= K G^T on the stored triangle: lane owns the columns c = lane + 32 q (its G[c] stays in
-    // registers), walks the rows i >= c; K[i] is a broadcast load
-    for (int c0 = 0; c0 < n; c0 += 32) {
-      const int c = c0 + lane;
-      const double2 gc = c < n ? G[c] : make_double2(0.0, 0.0);
-      double *sp = S + (c0 * (c0 + 1) / 2 + c);
-#pragma unroll 4
-      for (int i = c0; i < n; ++i) {
-        const double2 ki = K[i];
-        if (c <= i) *sp = *sp - (ki.x * gc.x + ki.y * gc.y);
-        sp += i + 1;
-      }
+    // Sigma -= K G^T on the stored triangle, element by element in packed order: 32 consecutive
+    // elements per step keep every lane busy (a column-per-lane walk idles half of them on the triangle);
+    // (row, column) of an element comes from a small table that stays in L1
+    for (int e = lane; e < tri; e += 32) {
+      const uchar2 ic = __ldg(p.tri_map + e);
+      const double2 ki = K[ic.x], gc = G[ic.y];
+      S[e] = S[e] - (ki.x * gc.x + ki.y * gc.y);
     }
     __syncwarp();
   }
