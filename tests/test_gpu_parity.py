@@ -190,6 +190,32 @@ def test_procedural_map_against_oracle_b(N, count, m, scans):
     g.close(); o.close()
 
 
+def test_robot_standing_on_a_mapped_landmark_nan_candidate_never_wins():
+    """a landmark that coincides with the robot has d = 0, so its Jacobian (slam.cpp:384-392) and its
+    Mahalanobis distance are NaN; arma::index_min's strict `<` scan never selects a NaN, whatever its index.
+    The NaN candidate here has a LOWER index than every true match."""
+    N, count = 300, 290
+    g, o, grid_w = _procedural_pair(N, count)
+    rng = np.random.default_rng(17)
+    k_nan = 0                                              # the robot is put exactly on this landmark
+    lx, ly = float(o.state[3 + 2 * k_nan]), float(o.state[4 + 2 * k_nan])
+    pose = np.array([0.4, lx, ly])
+    g.set_previous_xy(lx - 0.05, ly); o.set_prev(lx - 0.05, ly)
+    near, xy = _scan_inputs(o.state, count, grid_w, rng, 12, pose)
+    keep = near != k_nan
+    near, xy = near[keep], xy[keep]
+    assert (near > k_nan).all()
+    aG, cG, _ = g.scan(pose, xy)
+    o.predict(*pose)
+    aO = o.update_unknown(xy)
+    assert list(aG) == list(aO) == list(near)
+    assert cG == o.count == count
+    assert np.isfinite(g.state()).all()
+    assert rel_fro(g.state(), o.state) <= TOL
+    assert rel_fro(g.sigma(), o.sigma) <= TOL
+    g.close(); o.close()
+
+
 @pytest.mark.parametrize("threads,blocks", [(256, None), (64, 3), (256, 1)])
 def test_sequential_kernel_shapes(threads, blocks, monkeypatch):
     """both shapes of the sequential kernel (ekf_seq.cuh: 64 threads x up to 2 CTAs / SM for maps of one
@@ -232,3 +258,54 @@ def test_full_size_N10k_one_scan_against_oracle_b():
     P = g.sigma_block(0, 3, 0, 3)
     assert np.array_equal(P, P.T) and np.all(np.linalg.eigvalsh(P) > 0)
     g.close(); o.close()
+
+
+def test_maximum_size_N60k_properties():
+    """BASELINE config 5 (N = 60,000, n = 120,003; the stored triangle is 57.7 GB - oracle B cannot hold it on
+    the host): one scan with 16 re-sightings + 4 new landmarks, checked through size-independent properties:
+    the association is the expected one, the touched variances shrink, far-away blocks shrink only slightly,
+    the pose block stays symmetric positive definite, a second identical scan keeps the map size."""
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    if free < 70e9:
+        pytest.skip("needs 70 GB of free HBM")
+    N, count, m = 60000, 59990, 20
+    g = ekf_slam_b200.EkfSlam(n_landmarks=N)
+    grid_w = int(np.ceil(np.sqrt(count)))
+    g.fill_procedural(7, count, grid_w)
+    state = g.state()
+    rng = np.random.default_rng(23)
+    # the procedural field fills a 245-wide grid row by row: row 244 ends at x = 209, nothing lies beyond y = 244
+    assert grid_w == 245
+    pose = np.array([0.9, 215.3, 242.6])
+    g.set_previous_xy(pose[1] - 0.1, pose[2] + 0.05)
+    near, xy = _scan_inputs(state, count, grid_w, rng, m, pose)
+    fresh = np.array([[214.0, 246.0], [216.5, 246.3], [219.0, 246.1], [221.5, 246.4]])   # >= 2 m from any landmark
+    c, s_ = np.cos(pose[0]), np.sin(pose[0])
+    d = fresh - pose[1:]
+    xy[:4] = np.stack([c * d[:, 0] + s_ * d[:, 1], -s_ * d[:, 0] + c * d[:, 1]], axis=1)
+    blk = lambda k: g.sigma_block(3 + 2 * int(k), 5 + 2 * int(k), 3 + 2 * int(k), 5 + 2 * int(k))
+    before = {int(k): blk(k) for k in near[4:]}
+    far = [5, 30011, 59000]
+    far_before = {k: blk(k) for k in far}
+    cross_before = g.sigma_block(3 + 2 * 59000, 5 + 2 * 59000, 3 + 2 * 5, 5 + 2 * 5)
+    a, cnt, _ = g.scan(pose, xy)
+    assert list(a[:4]) == [count, count + 1, count + 2, count + 3]
+    assert list(a[4:]) == list(near[4:]) and cnt == count + 4
+    for k in near[4:]:
+        assert np.trace(blk(k)) < np.trace(before[int(k)])
+    for k in far:           # far away, correlated through the low-rank cross term only: the diagonal of
+        after = blk(k)      # Sigma - K S K^T can only shrink, and here only a little
+        assert np.all(np.diag(after) <= np.diag(far_before[k]))
+        assert np.allclose(after, far_before[k], rtol=0.1, atol=0)
+    assert not np.array_equal(g.sigma_block(3 + 2 * 59000, 5 + 2 * 59000, 3 + 2 * 5, 5 + 2 * 5), cross_before)
+    P = g.sigma_block(0, 3, 0, 3)
+    assert np.array_equal(P, P.T) and np.all(np.linalg.eigvalsh(P) > 0)
+    new_blk = blk(count)
+    assert np.all(np.linalg.eigvalsh(new_blk) > 0) and np.trace(new_blk) < 1.0      # the 1e7 prior is gone
+    st2 = g.state()
+    xy2 = _scan_inputs(st2, count + 4, grid_w, rng, m, st2[:3])[1]
+    a2, cnt2, _ = g.scan(st2[:3], xy2)
+    assert cnt2 == count + 4 and (np.asarray(a2) >= 0).all()
+    assert g.last_status() == 0
+    g.close()
