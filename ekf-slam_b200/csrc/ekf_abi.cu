@@ -54,6 +54,10 @@ struct ekf_filter {
   // staging for the host-pointer entry points
   unsigned char *io_dev = nullptr, *io_host = nullptr;   // inputs: pose | xy | ids | action
   unsigned char *res_dev = nullptr, *res_host = nullptr; // results: pose | cnt | status | assoc
+  // host-buffer scans hand their results back as soon as the sequential phase is done: the copy is
+  // enqueued between the last sequential launch and its covariance pass, the caller waits on this event
+  cudaEvent_t res_event = nullptr;
+  size_t res_pending = 0;    // bytes of results the next finishing sequential launch should copy out (0 = none)
   size_t io_cap = 0, res_cap = 0;
   double *scratch_dev = nullptr;  // block get/set staging
   size_t scratch_cap = 0;

@@ -45,6 +45,7 @@ int ekf_destroy(ekf_filter *f) {
     cudaFree(f->io_dev); cudaFree(f->res_dev); cudaFree(f->scratch_dev);
     if (f->io_host) cudaFreeHost(f->io_host);
     if (f->res_host) cudaFreeHost(f->res_host);
+    if (f->res_event) cudaEventDestroy(f->res_event);
     for (auto &e : f->ev) if (e) cudaEventDestroy(e);
     f->ev.clear();
     if (f->own_stream) cudaStreamDestroy(f->own_stream);
@@ -95,6 +96,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
 #define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(e_, #call); } while (0)
 
   CKC(cudaStreamCreateWithFlags(&f->own_stream, cudaStreamNonBlocking));
+  CKC(cudaEventCreateWithFlags(&f->res_event, cudaEventDisableTiming));
   f->stream = f->own_stream;
   const size_t panel_bytes = (size_t)f->n_pad * f->kmax * sizeof(double);
   CKC(cudaMalloc(&f->sigma, (size_t)f->sigma_elems * sizeof(double)));

@@ -2,6 +2,18 @@
 
 namespace {
 
+// status + results -> pinned host staging, then the event ekf_scan's caller waits on.  Enqueued BEFORE the
+// covariance pass of the scan's last chunk: association, pose and count do not depend on it.
+int results_out(ekf_filter *f) {
+  const size_t total = f->res_pending;
+  f->res_pending = 0;
+  CK(f, cudaMemcpyAsync(f->res_dev + ResLayout(0).status, f->status, sizeof(int), cudaMemcpyDeviceToDevice, f->stream));
+  CK(f, cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
+  CK(f, cudaMemcpyAsync(f->res_host, f->res_dev, total, cudaMemcpyDeviceToHost, f->stream));
+  CK(f, cudaEventRecord(f->res_event, f->stream));
+  return EKF_OK;
+}
+
 // Launches the sequential kernel for measurements [t0, t0+mc) of a scan and, when mc > 0, the
 // covariance pass for the 2*mc panel columns it produced.  All pointers are device pointers.
 int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, const double *xy_dev,
@@ -30,6 +42,10 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
                                     seq_smem_bytes(f->seq_threads), f->stream));
   f->launches++;
   if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
+  if (finish && f->res_pending) {                        // everything the caller reads back is final here
+    const int rco = results_out(f);
+    if (rco != EKF_OK) return rco;
+  }
   if (mc > 0) {
     DdParams dp{};
     dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
@@ -94,17 +110,21 @@ int scan_host(ekf_filter *f, const double *pose, int m, const double *xy, const 
     if (action) memcpy(f->io_host + in.action, action, (size_t)m);
   }
   CK(f, cudaMemcpyAsync(f->io_dev, f->io_host, in.total, cudaMemcpyHostToDevice, f->stream));
+  f->res_pending = res.total;
   rc = scan_device(f, pose ? reinterpret_cast<const double *>(f->io_dev + in.pose) : nullptr, m,
                    reinterpret_cast<const double *>(f->io_dev + in.xy),
                    ids ? reinterpret_cast<const int32_t *>(f->io_dev + in.ids) : nullptr,
                    action ? reinterpret_cast<const uint8_t *>(f->io_dev + in.action) : nullptr,
                    reinterpret_cast<int32_t *>(f->res_dev + res.assoc), reinterpret_cast<double *>(f->res_dev + res.pose),
                    reinterpret_cast<int *>(f->res_dev + res.cnt));
-  if (rc != EKF_OK) return rc;
-  CK(f, cudaMemcpyAsync(f->res_dev + res.status, f->status, sizeof(int), cudaMemcpyDeviceToDevice, f->stream));
-  CK(f, cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
-  CK(f, cudaMemcpyAsync(f->res_host, f->res_dev, res.total, cudaMemcpyDeviceToHost, f->stream));
-  CK(f, cudaStreamSynchronize(f->stream));
+  if (rc != EKF_OK) { f->res_pending = 0; return rc; }
+  if (f->res_pending) {                           // a scan without measurements has no finishing launch
+    rc = results_out(f);
+    if (rc != EKF_OK) return rc;
+  }
+  // the covariance pass of this scan may still be running: it is stream-ordered before anything that
+  // reads Sigma, and the next call's kernels queue up behind it
+  CK(f, cudaEventSynchronize(f->res_event));
   if (out_assoc && m > 0) memcpy(out_assoc, f->res_host + res.assoc, (size_t)4 * m);
   if (out_count) memcpy(out_count, f->res_host + res.cnt, 4);
   if (out_pose) memcpy(out_pose, f->res_host + res.pose, 24);

@@ -107,7 +107,11 @@ int ekf_update_unknown(ekf_filter *f, int32_t m, const double *xy, int32_t *out_
  * action_dev[m] or NULL, assoc_dev[m] or NULL.  Used by the throughput harness; errors latch. */
 int ekf_scan_dev(ekf_filter *f, const double *pose_dev, int32_t m, const double *xy_dev,
                  const int32_t *ids_dev, const uint8_t *action_dev, int32_t *assoc_dev);
-/* the same with HOST buffers (copies in, runs, copies assoc / count / pose back, syncs) */
+/* the same with HOST buffers: copies in, runs, copies assoc / count / pose / status back.  Returns as soon
+ * as those are final, i.e. after the sequential phase of the scan; the covariance pass of the scan may
+ * still be running on the handle's stream.  Nothing observable depends on that: every accessor and every
+ * later call is ordered behind it on the same stream (ekf_synchronize waits for it explicitly).  The
+ * same holds for ekf_predict / ekf_update_known / ekf_update_unknown. */
 int ekf_scan(ekf_filter *f, const double pose[3], int32_t m, const double *xy, const int32_t *ids,
              const uint8_t *action, int32_t *out_assoc, int32_t *out_count, double out_pose[3]);
 
