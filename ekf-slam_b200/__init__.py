@@ -96,6 +96,7 @@ def load() -> C.CDLL:
         "ekf_shard_sync_finish": (C.c_int, [vp]),
         "ekf_shard_scan_begin": (C.c_int, [vp, vp, i32, vp, vp, i32, C.POINTER(vp), i64p]),
         "ekf_shard_scan_finish": (C.c_int, [vp, vp, vp, vp, vp]),
+        "ekf_shard_scan_finish_ex": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int64, vp]),
         "ekf_landmarks_create": (C.c_int, [i32, i32, i32, i32, C.POINTER(vp)]),
         "ekf_landmarks_destroy": (C.c_int, [vp]),
         "ekf_landmarks_detect": (C.c_int, [vp, i32, C.POINTER(C.c_float), C.c_float, C.c_float, C.c_double, dp, ip, ip]),
@@ -329,11 +330,15 @@ class EkfSlam:
                     "ekf_shard_scan_begin")
         return int(ptr.value), int(cnt.value)
 
-    def shard_scan_finish(self, assoc_ptr: int = 0, done_ptr: int = 0, pose_ptr: int = 0, count_ptr: int = 0):
+    def shard_scan_finish(self, assoc_ptr: int = 0, done_ptr: int = 0, pose_ptr: int = 0, count_ptr: int = 0,
+                          results_dev: int = 0, results_host: int = 0, results_bytes: int = 0, results_event: int = 0):
+        """results_*: device block -> pinned host copy and event, enqueued before the covariance pass"""
         vp = C.c_void_p
-        self._check(self._L.ekf_shard_scan_finish(self._h, vp(assoc_ptr or None), vp(done_ptr or None),
-                                                  vp(pose_ptr or None), vp(count_ptr or None)),
-                    "ekf_shard_scan_finish")
+        self._check(self._L.ekf_shard_scan_finish_ex(self._h, vp(assoc_ptr or None), vp(done_ptr or None),
+                                                     vp(pose_ptr or None), vp(count_ptr or None),
+                                                     vp(results_dev or None), vp(results_host or None),
+                                                     results_bytes, vp(results_event or None)),
+                    "ekf_shard_scan_finish_ex")
 
     def storage(self):
         a, b = C.c_int64(0), C.c_int64(0)

@@ -88,7 +88,14 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
 
 int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, double *pose_out_dev,
                           int32_t *count_dev) {
+  return ekf_shard_scan_finish_ex(f, assoc_dev, done_dev, pose_out_dev, count_dev, nullptr, nullptr, 0, nullptr);
+}
+
+int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, double *pose_out_dev,
+                             int32_t *count_dev, const void *results_dev, void *results_host, int64_t results_bytes,
+                             void *results_event) {
   if (!shard_ok(f) || f->pend_m < 1) return EKF_ERR_INVALID;
+  if (results_bytes < 0 || (results_bytes > 0 && (!results_dev || !results_host))) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
   int rc = ensure_io(f, 1);
   if (rc != EKF_OK) return rc;
@@ -121,6 +128,10 @@ int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, 
                                     seq_smem_bytes(f->seq_threads), f->stream));
   f->launches++;
   if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
+  // association / done / pose / count are final here: hand them to the host before the covariance pass
+  if (results_bytes > 0)
+    CK(f, cudaMemcpyAsync(results_host, results_dev, (size_t)results_bytes, cudaMemcpyDeviceToHost, f->stream));
+  if (results_event) CK(f, cudaEventRecord((cudaEvent_t)results_event, f->stream));
   DdParams dp{};
   dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
   dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;

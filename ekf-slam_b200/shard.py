@@ -103,17 +103,68 @@ class _Driver:
             t0 += done
         return rounds
 
+    def _host_io(self, m):
+        """pinned staging for scan(): one H2D of (pose | xy), one D2H of (pose_after | count | done | assoc)"""
+        if getattr(self, "_io_m", -1) >= m:
+            return
+        self._io_m = m
+        self._h_in = torch.empty(3 + 2 * m, dtype=torch.float64, pin_memory=True)
+        self._d_in = torch.empty(3 + 2 * m, dtype=torch.float64, device=self.device)
+        self._h_ids = torch.empty(m, dtype=torch.int32, pin_memory=True)
+        self._d_ids = torch.empty(m, dtype=torch.int32, device=self.device)
+        self._d_res = torch.zeros(32 + 4 * m, dtype=torch.uint8, device=self.device)
+        self._h_res = torch.zeros(32 + 4 * m, dtype=torch.uint8, pin_memory=True)
+        self._r_pose = self._d_res[0:24].view(torch.float64)
+        self._r_cnt = self._d_res[24:28].view(torch.int32)
+        self._r_done = self._d_res[28:32].view(torch.int32)
+        self._r_assoc = self._d_res[32:32 + 4 * m].view(torch.int32)
+        self._res_ev = torch.cuda.Event()
+        self._res_ev.record(self.stream)          # creates the underlying cudaEvent_t
+
     def scan(self, pose, xy, ids=None):
-        """host arrays in, (assoc, count, pose_after, rounds) out"""
+        """host arrays in, (assoc, count, pose_after, rounds) out.  Per round: one pinned H2D copy, the
+        kernels + the exchange, one pinned D2H copy, one synchronise."""
         xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
+        m = len(xy)
         with torch.cuda.stream(self.stream):
-            pose_t = torch.from_numpy(np.ascontiguousarray(pose, dtype=np.float64)).to(self.device)
-            xy_t = torch.from_numpy(xy).to(self.device)
-            ids_t = None if ids is None else \
-                torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int32)).to(self.device)
-            assoc_t = torch.full((len(xy),), -7, dtype=torch.int32, device=self.device)
-            rounds = self._scan_dev(pose_t, xy_t, assoc_t, ids_t, True)
-            return assoc_t.cpu().numpy(), int(self._cnt.item()), self._pose_out.cpu().numpy(), rounds
+            self._host_io(m)
+            hin = self._h_in.numpy()
+            hin[:3] = np.asarray(pose, dtype=np.float64)
+            hin[3:3 + 2 * m] = xy.ravel()
+            self._d_in[:3 + 2 * m].copy_(self._h_in[:3 + 2 * m], non_blocking=True)
+            pose_t, xy_t = self._d_in[:3], self._d_in[3:3 + 2 * m].view(m, 2)
+            ids_t = None
+            if ids is not None:
+                self._h_ids.numpy()[:m] = np.asarray(ids, dtype=np.int32)
+                self._d_ids[:m].copy_(self._h_ids[:m], non_blocking=True)
+                ids_t = self._d_ids[:m]
+            self._r_assoc.fill_(-7)
+            hres = self._h_res.numpy()
+            t0, first, rounds = 0, True, 0
+            while t0 < m:
+                rem = m - t0
+                bufs = [h.shard_scan_begin(pose_t.data_ptr() if first else 0, rem, xy_t[t0:].data_ptr(),
+                                           ids_t[t0:].data_ptr() if ids_t is not None else 0, rem <= MAX_ROUND)
+                        for h in self.handles()]
+                self.exchange(bufs)
+                hs = self.handles()
+                for q, h in enumerate(hs):
+                    tail = q == len(hs) - 1       # the last handle's finish hands the results to the host
+                    h.shard_scan_finish(self._r_assoc[t0:].data_ptr(), self._r_done.data_ptr(),
+                                        self._r_pose.data_ptr(), self._r_cnt.data_ptr(),
+                                        self._d_res.data_ptr() if tail else 0, self._h_res.data_ptr() if tail else 0,
+                                        self._d_res.numel() if tail else 0, self._res_ev.cuda_event if tail else 0)
+                # results are final after the sequential phase; the covariance pass keeps running while the
+                # host reads them and prepares the next round / scan
+                self._res_ev.synchronize()
+                rounds += 1
+                first = False
+                done = int(hres[28:32].view(np.int32)[0])
+                if done == 0 and rounds > 4 * m + 4:
+                    raise RuntimeError("sharded scan makes no progress")
+                t0 += done
+            assoc = hres[32:32 + 4 * m].view(np.int32).copy()
+            return assoc, int(hres[24:28].view(np.int32)[0]), hres[0:24].view(np.float64).copy(), rounds
 
 
 class LocalShards(_Driver):

@@ -177,6 +177,14 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
                          const int32_t *ids_dev, int32_t last_round, double **xchg_dev, int64_t *xchg_doubles);
 int ekf_shard_scan_finish(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, double *pose_out_dev,
                           int32_t *count_dev);
+/* the same; in addition, right after the sequential phase (when association, done, pose and count are
+ * final) and BEFORE the covariance pass it enqueues a device-to-host copy of results_bytes bytes from
+ * results_dev to results_host (pinned; 0 bytes = none) and records results_event (a cudaEvent_t, or NULL)
+ * on the handle's stream: a host that waits on the event instead of the stream prepares the next scan
+ * while the pass runs. */
+int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_dev, double *pose_out_dev,
+                             int32_t *count_dev, const void *results_dev, void *results_host, int64_t results_bytes,
+                             void *results_event);
 
 /* ---- batched mode: B independent small filters, one CTA each, Sigma in shared memory ---------
  * (BASELINE config 3).  Each filter runs the whole sensor callback of the reference
