@@ -95,6 +95,8 @@ def load() -> C.CDLL:
         "ekf_shard_sync_begin": (C.c_int, [vp, C.POINTER(vp), i64p]),
         "ekf_shard_sync_finish": (C.c_int, [vp]),
         "ekf_shard_scan_begin": (C.c_int, [vp, vp, i32, vp, vp, i32, C.POINTER(vp), i64p]),
+        "ekf_shard_peer_export": (C.c_int, [vp, vp, C.POINTER(vp), i64p]),
+        "ekf_shard_peer_attach": (C.c_int, [vp, i32, vp, vp]),
         "ekf_shard_scan_finish": (C.c_int, [vp, vp, vp, vp, vp]),
         "ekf_shard_scan_finish_ex": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int64, vp]),
         "ekf_landmarks_create": (C.c_int, [i32, i32, i32, i32, C.POINTER(vp)]),
@@ -317,7 +319,7 @@ class EkfSlam:
     def shard_sync_begin(self):
         ptr, cnt = C.c_void_p(), C.c_int64(0)
         self._check(self._L.ekf_shard_sync_begin(self._h, C.byref(ptr), C.byref(cnt)), "ekf_shard_sync_begin")
-        return int(ptr.value), int(cnt.value)
+        return int(ptr.value or 0), int(cnt.value)
 
     def shard_sync_finish(self):
         self._check(self._L.ekf_shard_sync_finish(self._h), "ekf_shard_sync_finish")
@@ -328,7 +330,21 @@ class EkfSlam:
         self._check(self._L.ekf_shard_scan_begin(self._h, vp(pose_ptr or None), m, vp(xy_ptr), vp(ids_ptr or None),
                                                  1 if last_round else 0, C.byref(ptr), C.byref(cnt)),
                     "ekf_shard_scan_begin")
-        return int(ptr.value), int(cnt.value)
+        return int(ptr.value or 0), int(cnt.value)
+
+    def shard_peer_export(self):
+        """(64-byte CUDA IPC handle, device pointer, bytes) of this rank's peer-visible exchange region"""
+        buf = C.create_string_buffer(64)
+        base, nbytes = C.c_void_p(0), C.c_int64(0)
+        self._check(self._L.ekf_shard_peer_export(self._h, buf, C.byref(base), C.byref(nbytes)),
+                    "ekf_shard_peer_export")
+        return bytes(buf.raw), int(base.value), int(nbytes.value)
+
+    def shard_peer_attach(self, peer_rank: int, ipc_handle: bytes = None, base_ptr: int = 0):
+        """another rank's region: its IPC handle (other process) or its device pointer (same process)"""
+        buf = C.create_string_buffer(ipc_handle, 64) if ipc_handle is not None else None
+        self._check(self._L.ekf_shard_peer_attach(self._h, peer_rank, buf, C.c_void_p(base_ptr or None)),
+                    "ekf_shard_peer_attach")
 
     def shard_scan_finish(self, assoc_ptr: int = 0, done_ptr: int = 0, pose_ptr: int = 0, count_ptr: int = 0,
                           results_dev: int = 0, results_host: int = 0, results_bytes: int = 0, results_event: int = 0):

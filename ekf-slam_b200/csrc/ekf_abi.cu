@@ -38,6 +38,15 @@ struct ekf_filter {
   double *guess_part_d = nullptr;        // sharded: per-slice partial candidates of the speculative association
   int *guess_part_k = nullptr;
   unsigned int *guess_ticket = nullptr;
+  // sharded, peer-memory exchange (ekf_shard_peer_*): one allocation = [cols round-parity 0][cols parity 1][flags]
+  unsigned char *xchg = nullptr;
+  size_t xchg_cols_bytes = 0;             // bytes of ONE column buffer
+  unsigned char *peer_base[16] = {};      // the same region of every rank (own entry = xchg), peer-mapped
+  void *peer_ipc[16] = {};                // regions opened with cudaIpcOpenMemHandle (closed at destroy)
+  int peers_attached = 0;
+  unsigned long long xchg_round = 0;      // rounds pushed so far
+  unsigned int *push_done = nullptr;      // last-CTA counter of the push kernel
+  int pend_peer = 0;                      // the pending round was exchanged through peer memory
   // the round opened by ekf_shard_scan_begin
   int pend_m = -1, pend_finish = 0;
   const double *pend_xy = nullptr;

@@ -41,6 +41,9 @@ int ekf_destroy(ekf_filter *f) {
     cudaFree(f->Pp); cudaFree(f->cnt); cudaFree(f->status);   // D lives in the Pp allocation
     cudaFree(f->cols); cudaFree(f->guess); cudaFree(f->done_dev);
     cudaFree(f->guess_part_d); cudaFree(f->guess_part_k); cudaFree(f->guess_ticket);
+    for (int q = 0; q < 16; ++q)
+      if (f->peer_ipc[q]) cudaIpcCloseMemHandle(f->peer_ipc[q]);
+    cudaFree(f->xchg); cudaFree(f->push_done);
     cudaFree(f->prev_xy); cudaFree(f->bar); cudaFree(f->slot_d); cudaFree(f->slot_k); cudaFree(f->slot_rec);
     cudaFree(f->io_dev); cudaFree(f->res_dev); cudaFree(f->scratch_dev);
     if (f->io_host) cudaFreeHost(f->io_host);

@@ -18,9 +18,62 @@ int shard_buffers(ekf_filter *f) {
   return EKF_OK;
 }
 
+// the peer-visible exchange region: two column buffers (round parity) + the arrival flags
+int shard_xchg_region(ekf_filter *f) {
+  if (f->xchg) return EKF_OK;
+  f->xchg_cols_bytes = (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double);
+  const size_t total = 2 * f->xchg_cols_bytes + kMaxPeers * sizeof(unsigned long long);
+  CK(f, cudaMalloc(&f->xchg, total));
+  CK(f, cudaMemset(f->xchg, 0, total));
+  CK(f, cudaMalloc(&f->push_done, sizeof(unsigned int)));
+  CK(f, cudaMemset(f->push_done, 0, sizeof(unsigned int)));
+  f->peer_base[f->cfg.shard_rank] = f->xchg;
+  f->peers_attached = 1;
+  return EKF_OK;
+}
+bool shard_peer_mode(const ekf_filter *f) { return f->xchg != nullptr && f->peers_attached == f->cfg.shard_count; }
+
 }  // namespace
 
 extern "C" {
+
+int ekf_shard_peer_export(ekf_filter *f, void *ipc_handle_64, void **local_base, int64_t *region_bytes) {
+  if (!shard_ok(f) || f->cfg.shard_count > kMaxPeers) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  int rc = shard_xchg_region(f);
+  if (rc != EKF_OK) return rc;
+  if (ipc_handle_64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    cudaIpcMemHandle_t h;
+    CK(f, cudaIpcGetMemHandle(&h, f->xchg));
+    memcpy(ipc_handle_64, &h, 64);
+  }
+  if (local_base) *local_base = f->xchg;
+  if (region_bytes) *region_bytes = (int64_t)(2 * f->xchg_cols_bytes + kMaxPeers * sizeof(unsigned long long));
+  return EKF_OK;
+}
+
+int ekf_shard_peer_attach(ekf_filter *f, int32_t peer_rank, const void *ipc_handle_64, void *same_process_base) {
+  if (!shard_ok(f) || peer_rank < 0 || peer_rank >= f->cfg.shard_count || peer_rank == f->cfg.shard_rank)
+    return EKF_ERR_INVALID;
+  if ((ipc_handle_64 == nullptr) == (same_process_base == nullptr)) return EKF_ERR_INVALID;   // exactly one
+  DeviceGuard guard(f->device);
+  int rc = shard_xchg_region(f);
+  if (rc != EKF_OK) return rc;
+  if (f->peer_base[peer_rank]) return EKF_ERR_INVALID;        // already attached
+  if (ipc_handle_64) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle_64, 64);
+    void *p = nullptr;
+    CK(f, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    f->peer_ipc[peer_rank] = p;
+    f->peer_base[peer_rank] = static_cast<unsigned char *>(p);
+  } else {
+    f->peer_base[peer_rank] = static_cast<unsigned char *>(same_process_base);
+  }
+  f->peers_attached++;
+  return EKF_OK;
+}
 
 int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t *stored_doubles) {
   if (!f) return EKF_ERR_INVALID;
@@ -75,14 +128,29 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
   // test-only fault injection: forget the speculation for one sighting so that the stop / resume path runs
   const int drop = env_int("EKF_SHARD_DROP_GUESS", -1);
   if (drop >= 0 && drop < mc) CK(f, cudaMemsetAsync(f->guess + drop, 0xFF, sizeof(int), f->stream));
-  shard_extract_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc,
-                                                                   f->cols);
+  f->pend_peer = shard_peer_mode(f) ? 1 : 0;
+  if (f->pend_peer) {
+    // extraction + exchange + arrival flags in one kernel over peer memory: nothing left for the caller
+    f->xchg_round++;
+    PeerTable pt{};
+    pt.count = f->cfg.shard_count; pt.self = f->cfg.shard_rank;
+    const size_t par_off = (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes;
+    for (int q = 0; q < pt.count; ++q) {
+      pt.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
+      pt.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
+    }
+    shard_push_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt,
+                                                                  f->xchg_round, f->push_done);
+  } else {
+    shard_extract_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc,
+                                                                     f->cols);
+  }
   f->launches += 2;
   CK(f, cudaGetLastError());
   f->pend_m = mc; f->pend_xy = xy_dev; f->pend_ids = ids_dev;
   f->pend_finish = (last_round && mc == m) ? 1 : 0;
-  *xchg_dev = f->cols;
-  *xchg_doubles = (int64_t)mc * f->n_pad * 2;
+  *xchg_dev = f->pend_peer ? nullptr : f->cols;
+  *xchg_doubles = f->pend_peer ? 0 : (int64_t)mc * f->n_pad * 2;
   return EKF_OK;
 }
 
@@ -112,6 +180,14 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   sp.pose_out = pose_out_dev ? pose_out_dev : reinterpret_cast<double *>(f->res_dev + res.pose);
   sp.cnt_out = count_dev ? count_dev : reinterpret_cast<int *>(f->res_dev + res.cnt);
   sp.side_mode = 1; sp.cols = f->cols; sp.guess = f->guess;
+  if (f->pend_peer) {
+    // every rank's part of this round must have landed in this rank's buffer before it is read
+    sp.cols = reinterpret_cast<const double *>(f->xchg + (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes);
+    shard_wait_peers_kernel<<<1, 32, 0, f->stream>>>(
+        reinterpret_cast<const unsigned long long *>(f->xchg + 2 * f->xchg_cols_bytes), f->cfg.shard_count,
+        f->xchg_round, f->status);
+    f->launches++;
+  }
   sp.done_out = done_dev ? done_dev : f->done_dev;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;

@@ -167,6 +167,72 @@ __global__ void shard_extract_cols_kernel(const double *sigma, EkfLay lay, int n
   }
 }
 
+// ---- the same exchange as ONE kernel over peer memory (NVLink / NVSwitch): no collective call -------
+// Every used element of the column buffer has exactly one owner (the rank that stores the Sigma row it
+// comes from).  The owner reads it and STORES it straight into the column buffer of every rank - its own
+// and, through peer-mapped pointers (CUDA IPC between processes), the others' - so the "all-reduce" is
+// R - 1 remote stores per owned element and no reduction at all.  The last CTA to finish publishes this
+// rank's arrival flag in every rank's flag array (system-scope release after the data); the consumer
+// side is shard_wait_peers_kernel right before the sequential kernel.  Buffers alternate by round parity:
+// a fast rank may already push round r + 1 while a slow one still reads round r.
+constexpr int kMaxPeers = 16;
+struct PeerTable {
+  int count, self;
+  double *cols[kMaxPeers];                 // this round's column buffer of every rank
+  unsigned long long *flags[kMaxPeers];    // flag array of every rank: flags[q][g] = rounds rank g has pushed to q
+};
+__global__ void shard_push_cols_kernel(const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m,
+                                       PeerTable peers, unsigned long long round_no, unsigned int *done_ctas) {
+  const int64_t total = (int64_t)m * n_pad;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int slot = (int)(e / n_pad), i = (int)(e % n_pad);
+    const int j = guess[slot];
+    if (j < 0 || j >= N) continue;
+    const int a = 4 + 2 * j;
+    double2 v;
+    if (i > a + 1) {
+      if (!ekf_lay_owns_row(lay, i)) continue;
+      v = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a));
+    } else if (i < a) {
+      if (!ekf_lay_owns_row(lay, a)) continue;
+      v.x = sigma[ekf_lay_elem(lay, a, i)];
+      v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
+    } else {
+      continue;                            // the landmark's own 2 x 2 block comes from D, not from here
+    }
+    for (int q = 0; q < peers.count; ++q) *reinterpret_cast<double2 *>(peers.cols[q] + e * 2) = v;
+  }
+  // arrival: every CTA's stores are visible system-wide before the flags move
+  __threadfence_system();
+  __syncthreads();
+  __shared__ unsigned int s_prev;
+  if (threadIdx.x == 0) s_prev = atomicAdd(done_ctas, 1u);
+  __syncthreads();
+  if (s_prev == gridDim.x - 1) {
+    if (threadIdx.x == 0) *done_ctas = 0;                    // ready for the next launch
+    __threadfence_system();
+    if ((int)threadIdx.x < peers.count) {
+      unsigned long long *dst = peers.flags[threadIdx.x] + peers.self;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(round_no) : "memory");
+    }
+  }
+}
+// consumer side: wait until every rank has pushed round `round_no` into this rank's buffer.  Bounded: a peer
+// that never arrives (crashed process) latches kErrPeerTimeout after ~10 s instead of hanging the GPU.
+constexpr int kErrPeerTimeout = 5;         // EKF_ERR_CUDA: the exchange did not complete
+__global__ void shard_wait_peers_kernel(const unsigned long long *flags, int count, unsigned long long round_no,
+                                        int *status) {
+  if ((int)threadIdx.x >= count) return;
+  unsigned long long t0, now, v;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + threadIdx.x) : "memory");
+    if (v >= round_no) return;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+  } while (now - t0 < 10000000000ull);
+  atomicMax(status, kErrPeerTimeout);
+}
+
 // ---- side state <-> Sigma -----------------------------------------------------------------------
 // side[0 .. 4 n_pad) = Pp rows (x, y, z, 0), side[4 n_pad ..) = D blocks (aa, ba, bb, 0): this rank's
 // owned rows, zero elsewhere (summed over the ranks afterwards)

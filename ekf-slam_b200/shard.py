@@ -170,16 +170,25 @@ class _Driver:
 class LocalShards(_Driver):
     """R row shards of one map as R handles on one GPU (test / single-GPU emulation of R ranks)."""
 
-    def __init__(self, n_landmarks: int, shards: int, device_index: int = 0, **kw):
+    def __init__(self, n_landmarks: int, shards: int, device_index: int = 0, peer: bool = False, **kw):
         self.hs = [EkfSlam(n_landmarks=n_landmarks, device=device_index, shard_rank=r, shard_count=shards, **kw)
                    for r in range(shards)]
         self._setup(torch.device("cuda", device_index))
         self.n = self.hs[0].n
+        if peer and shards > 1:
+            # the peer-memory exchange with plain device pointers: every handle stores into every handle's region
+            bases = [h.shard_peer_export()[1] for h in self.hs]
+            for r, h in enumerate(self.hs):
+                for q, b in enumerate(bases):
+                    if q != r:
+                        h.shard_peer_attach(q, base_ptr=b)
 
     def handles(self):
         return self.hs
 
     def exchange(self, bufs):
+        if all(c == 0 for (_, c) in bufs):
+            return                                   # delivered through peer memory by the begin kernels
         ts = [alias(p, c, self.device) for (p, c) in bufs]
         total = ts[0].clone()
         for t in ts[1:]:
@@ -211,20 +220,37 @@ class LocalShards(_Driver):
 
 
 class ShardedEkf(_Driver):
-    """This process' row shard of one map in a torch.distributed job (NCCL all-reduce per round)."""
+    """This process' row shard of one map in a torch.distributed job.  The per-round exchange goes through
+    peer memory (CUDA IPC over NVLink: the begin kernel stores this rank's columns into every rank's buffer)
+    when peer=True, else through an NCCL all-reduce; the rare side-state sync always uses the all-reduce."""
 
-    def __init__(self, n_landmarks: int, rank: int, world: int, device_index: int, stream=None, group=None, **kw):
+    def __init__(self, n_landmarks: int, rank: int, world: int, device_index: int, stream=None, group=None,
+                 peer: bool = None, **kw):
+        import os
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.h = EkfSlam(n_landmarks=n_landmarks, device=device_index, shard_rank=rank, shard_count=world, **kw)
         self._setup(torch.device("cuda", device_index), stream)
         self.n = self.h.n
+        if peer is None:
+            peer = os.environ.get("EKF_SHARD_PEER", "1") != "0"
+        self.peer = bool(peer) and world > 1
+        if self.peer:
+            handle, _, _ = self.h.shard_peer_export()
+            everyone = [None] * world
+            dist.all_gather_object(everyone, handle, group=group)
+            for q, hq in enumerate(everyone):
+                if q != rank:
+                    self.h.shard_peer_attach(q, ipc_handle=hq)
+            dist.barrier(group=group)          # every rank has every region mapped before the first push
 
     def handles(self):
         return [self.h]
 
     def exchange(self, bufs):
         (p, c), = bufs
+        if c == 0:
+            return                                   # delivered through peer memory by the begin kernel
         self.dist.all_reduce(alias(p, c, self.device), op=self.dist.ReduceOp.SUM, group=self.group)
 
     def close(self):

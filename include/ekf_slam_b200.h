@@ -171,6 +171,16 @@ int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t ma
  * The ordinary ekf_scan / ekf_update_* entry points return EKF_ERR_INVALID on a sharded handle;
  * ekf_get_sigma_block returns 0 for entries stored by another rank (sum over ranks = Sigma). */
 int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t *stored_doubles);
+/* Optional: the per-scan exchange over peer memory instead of the caller's all-reduce.  Every rank exports
+ * its exchange region (a CUDA IPC handle for other processes, the plain device pointer for handles of the
+ * same process) and attaches every other rank's (exactly one of ipc_handle_64 / same_process_base per
+ * call).  Once all shard_count - 1 peers are attached, ekf_shard_scan_begin extracts AND delivers in one
+ * kernel - every rank stores the Sigma columns it owns straight into every rank's buffer over NVLink and
+ * raises an arrival flag there - and returns *xchg_doubles = 0: there is nothing left to reduce;
+ * ekf_shard_scan_finish waits for the flags on the device.  A peer that never arrives latches EKF_ERR_CUDA
+ * after 10 s instead of hanging.  ekf_shard_sync_* still uses the caller's all-reduce (rare). */
+int ekf_shard_peer_export(ekf_filter *f, void *ipc_handle_64, void **local_base, int64_t *region_bytes);
+int ekf_shard_peer_attach(ekf_filter *f, int32_t peer_rank, const void *ipc_handle_64, void *same_process_base);
 int ekf_shard_sync_begin(ekf_filter *f, double **xchg_dev, int64_t *xchg_doubles);
 int ekf_shard_sync_finish(ekf_filter *f);
 int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const double *xy_dev,

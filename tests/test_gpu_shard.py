@@ -23,10 +23,10 @@ def _scan_inputs(state, count, rng, m, pose):
     return near.astype(np.int32), xy
 
 
-def _pair(N, count, shards, seed=7):
+def _pair(N, count, shards, seed=7, peer=False):
     import struct_oracle as so
     from ekf_slam_b200 import shard
-    g = shard.LocalShards(N, shards)
+    g = shard.LocalShards(N, shards, peer=peer)
     grid_w = int(np.ceil(np.sqrt(count)))
     g.fill_procedural(seed, count, grid_w)
     g.sync()
@@ -69,6 +69,19 @@ def _drive(g, o, count, grid_w, m, scans, new_in_last=0, expect_rounds=None, res
 def test_sharded_map_against_oracle_b(shards):
     g, o, grid_w = _pair(300, 290, shards)
     _drive(g, o, 290, grid_w, 20, 4, new_in_last=4, expect_rounds=1)
+    g.close(); o.close()
+
+
+@pytest.mark.parametrize("shards", [2, 3])
+def test_peer_memory_exchange_against_oracle_b(shards, monkeypatch):
+    """the per-round exchange as one kernel over peer memory (every shard stores its columns into every
+    shard's buffer and raises arrival flags) instead of the caller's all-reduce; includes the stop / resume
+    path, which re-pushes into the other parity buffer"""
+    g, o, grid_w = _pair(300, 290, shards, peer=True)
+    _drive(g, o, 290, grid_w, 20, 5, new_in_last=4, expect_rounds=1)
+    monkeypatch.setenv("EKF_SHARD_DROP_GUESS", "5")
+    _drive(g, o, 294, grid_w, 20, 2)
+    assert g.hs[0].last_status() == 0
     g.close(); o.close()
 
 
