@@ -7,6 +7,10 @@ struct ekf_batch {
   double *sigma = nullptr, *mu = nullptr, *prev = nullptr;
   int *cnt = nullptr, *status = nullptr;
   uchar2 *tri_map = nullptr;     // (row, column) of every packed lower-triangle element
+  ushort4 *blk_map = nullptr;    // 2x2 blocks of the stored triangle (BatchParams::blk_map)
+  int nblk = 0;
+  unsigned short *soff = nullptr;   // shared-memory offset of every packed element (layout of this handle's variant)
+  int variant = 0;               // bits 0-1: downdate shape DD (0, 1, 2), bit 2: one-pass association, bit 3: 20 CTAs/SM
   // staging for the host-pointer step
   unsigned char *io_dev = nullptr, *io_host = nullptr, *res_dev = nullptr, *res_host = nullptr;
   size_t io_cap = 0, res_cap = 0;
@@ -16,6 +20,8 @@ struct ekf_batch {
 };
 
 namespace {
+
+constexpr int BATCH_DEFAULT_VARIANT = 13;   // 20 CTAs/SM, one-pass association, 2x2-block downdate (measured best)
 
 #define CKB(b, call)                                                               \
   do {                                                                             \
@@ -33,11 +39,21 @@ int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, con
   p.B = b->B; p.N = b->N; p.n = b->n; p.tri = b->tri;
   p.q_noise = b->cfg.q_noise; p.r_noise = b->cfg.r_noise; p.thr = b->cfg.mah_threshold;
   p.sigma = b->sigma; p.mu = b->mu; p.prev = b->prev; p.cnt = b->cnt; p.status = b->status;
-  p.tri_map = b->tri_map;
+  p.tri_map = b->tri_map; p.blk_map = b->blk_map; p.nblk = b->nblk; p.soff = b->soff;
   p.pose = poses; p.xy = xy; p.ids = ids; p.m_count = m_count; p.m = m;
   p.assoc_out = assoc; p.cnt_out = count; p.pose_out = pose_out;
-  if (batch_smem_bytes(b->n, m) > 200 * 1024) return EKF_ERR_INVALID;   // m beyond the per-CTA shared memory
-  ekf_batch_kernel<<<b->B, kBatchThreads, batch_smem_bytes(b->n, m), b->stream>>>(p);
+  const size_t smem = batch_smem_bytes(b->n, m, b->variant & 3);
+  if (smem > 200 * 1024) return EKF_ERR_INVALID;   // m beyond the per-CTA shared memory
+#define EKF_BATCH_CASE(V, MINB, ONE, DD) \
+  case V: ekf_batch_kernel<MINB, ONE, DD><<<b->B, kBatchThreads, smem, b->stream>>>(p); break;
+  switch (b->variant) {
+    EKF_BATCH_CASE(0, 16, false, 0)  EKF_BATCH_CASE(1, 16, false, 1)  EKF_BATCH_CASE(2, 16, false, 2)
+    EKF_BATCH_CASE(4, 16, true, 0)   EKF_BATCH_CASE(5, 16, true, 1)   EKF_BATCH_CASE(6, 16, true, 2)
+    EKF_BATCH_CASE(8, 20, false, 0)  EKF_BATCH_CASE(9, 20, false, 1)  EKF_BATCH_CASE(10, 20, false, 2)
+    EKF_BATCH_CASE(12, 20, true, 0)  EKF_BATCH_CASE(13, 20, true, 1)  EKF_BATCH_CASE(14, 20, true, 2)
+    default: return EKF_ERR_INVALID;
+  }
+#undef EKF_BATCH_CASE
   b->launches++;
   CKB(b, cudaGetLastError());
   return EKF_OK;
@@ -84,7 +100,7 @@ int ekf_batch_destroy(ekf_batch *b) {
   {
     DeviceGuard guard(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
-    cudaFree(b->sigma); cudaFree(b->mu); cudaFree(b->prev); cudaFree(b->cnt); cudaFree(b->status); cudaFree(b->tri_map);
+    cudaFree(b->sigma); cudaFree(b->mu); cudaFree(b->prev); cudaFree(b->cnt); cudaFree(b->status); cudaFree(b->tri_map); cudaFree(b->blk_map); cudaFree(b->soff);
     cudaFree(b->io_dev); cudaFree(b->res_dev);
     if (b->io_host) cudaFreeHost(b->io_host);
     if (b->res_host) cudaFreeHost(b->res_host);
@@ -131,6 +147,27 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
       for (int c = 0; c <= i; ++c) map[e++] = make_uchar2((unsigned char)i, (unsigned char)c);
     CKC(cudaMalloc(&b->tri_map, (size_t)b->tri * sizeof(uchar2)));
     CKC(cudaMemcpy(b->tri_map, map.data(), (size_t)b->tri * sizeof(uchar2), cudaMemcpyHostToDevice));
+    std::vector<ushort4> blk;
+    for (int i0 = 0; i0 < b->n; i0 += 2)
+      for (int j0 = 0; j0 <= i0; j0 += 2) {
+        const bool row1 = i0 + 1 < b->n;
+        const int mask = 1 | (j0 + 1 <= i0 ? 2 : 0) | (row1 ? 4 | 8 : 0);   // (i0+1, j0+1) is stored whenever row i0+1 is
+        blk.push_back(make_ushort4((unsigned short)i0, (unsigned short)j0,
+                                   (unsigned short)(batch_row_off(i0) + j0), (unsigned short)mask));
+      }
+    b->nblk = (int)blk.size();
+    b->variant = BATCH_DEFAULT_VARIANT;
+    if (const char *v = getenv("EKF_BATCH_VARIANT")) b->variant = atoi(v) & 15;   // development override
+    if ((b->variant & 3) == 3) b->variant &= ~1;
+    if (b->N > 32) b->variant &= ~4;                                               // one-pass needs a lane per landmark
+    std::vector<unsigned short> soff((size_t)b->tri);
+    for (size_t q = 0; q < soff.size(); ++q)
+      soff[q] = (unsigned short)((b->variant & 3) == 2 ? batch_tile_idx(map[q].x, map[q].y)
+                                                       : batch_row_off(map[q].x) + map[q].y);
+    CKC(cudaMalloc(&b->soff, soff.size() * sizeof(unsigned short)));
+    CKC(cudaMemcpy(b->soff, soff.data(), soff.size() * sizeof(unsigned short), cudaMemcpyHostToDevice));
+    CKC(cudaMalloc(&b->blk_map, blk.size() * sizeof(ushort4)));
+    CKC(cudaMemcpy(b->blk_map, blk.data(), blk.size() * sizeof(ushort4), cudaMemcpyHostToDevice));
   }
   CKC(cudaMemsetAsync(b->sigma, 0, sig_bytes, b->stream));
   CKC(cudaMemsetAsync(b->mu, 0, (size_t)b->B * b->n * sizeof(double), b->stream));
@@ -141,10 +178,16 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
       b->sigma, b->B, b->n, b->tri, cfg->prior);   // slam.cpp:128-132
   b->launches++;
   CKC(cudaGetLastError());
-  CKC(cudaFuncSetAttribute(ekf_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           200 * 1024));
-  CKC(cudaFuncSetAttribute(ekf_batch_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+#define EKF_BATCH_ATTR(MINB, ONE, DD)                                                                          \
+  CKC(cudaFuncSetAttribute(ekf_batch_kernel<MINB, ONE, DD>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
+                           200 * 1024));                                                                       \
+  CKC(cudaFuncSetAttribute(ekf_batch_kernel<MINB, ONE, DD>, cudaFuncAttributePreferredSharedMemoryCarveout,    \
                            cudaSharedmemCarveoutMaxShared));
+  EKF_BATCH_ATTR(16, false, 0) EKF_BATCH_ATTR(16, false, 1) EKF_BATCH_ATTR(16, false, 2)
+  EKF_BATCH_ATTR(16, true, 0)  EKF_BATCH_ATTR(16, true, 1)  EKF_BATCH_ATTR(16, true, 2)
+  EKF_BATCH_ATTR(20, false, 0) EKF_BATCH_ATTR(20, false, 1) EKF_BATCH_ATTR(20, false, 2)
+  EKF_BATCH_ATTR(20, true, 0)  EKF_BATCH_ATTR(20, true, 1)  EKF_BATCH_ATTR(20, true, 2)
+#undef EKF_BATCH_ATTR
   CKC(cudaStreamSynchronize(b->stream));
 #undef CKC
   *out = b;

@@ -30,6 +30,10 @@ struct BatchParams {
   int *cnt;
   int *status;             // latched error (max over filters)
   const uchar2 *tri_map;   // [tri] (row, column) of packed lower-triangle element e (n <= 131 < 256)
+  const ushort4 *blk_map;  // [nblk] 2x2 blocks of the stored triangle: (row i0, column j0, packed index of (i0, j0),
+                           // mask of the block's stored elements: 1 (i0,j0) 2 (i0,j0+1) 4 (i0+1,j0) 8 (i0+1,j0+1))
+  int nblk;
+  const unsigned short *soff;   // [tri] shared-memory offset (batch_row_off(row) + column) of packed element e
   // this step (device pointers)
   const double *pose;      // [B][3] (theta, x, y) composed odometry pose
   const double *xy;        // [B][m][2]
@@ -42,11 +46,59 @@ struct BatchParams {
 };
 
 constexpr int kBatchThreads = 32;
+// Kernel variants (template parameters; ekf_abi_batch.inl picks one per handle, EKF_BATCH_VARIANT overrides):
+//   MINB     resident CTAs per SM the register allocation is sized for (16: 128 registers, 20: 96)
+//   ONEPASS  every lane evaluates at most one candidate landmark (N <= 32): no loop-carried best-candidate record
+//   DD       rank-2 downdate Sigma -= K G^T of the stored triangle in shared memory:
+//            0  element by element in packed order (row / column table)
+//            1  2x2 blocks, K rows / G columns loaded once per block, 128-bit accesses
+//            2  8x8 tiles on the fp64 tensor path (DMMA m8n8k4, k = 2 of 4 used), Sigma stored tile by tile
+//               in accumulator-fragment order: one conflict-free 128-bit load + store per lane per tile
 constexpr int kBatchErrCapacity = 2, kBatchErrBadId = 4;   // ekf_status values
 
-__host__ __device__ inline size_t batch_smem_bytes(int n, int m) {
-  const size_t tri = (size_t)n * (n + 1) / 2;
-  return (tri + (size_t)n + 4 * (size_t)n + 2 * (size_t)m + 8) * sizeof(double);
+// Shared-memory layout of one filter's covariance: the stored triangle row by row, every row starting on a
+// 16-byte boundary (rows 2k and 2k+1 both occupy 2k+2 doubles), so that the two adjacent columns of a 2x2
+// block are one aligned 128-bit access and consecutive lanes' blocks are consecutive.  Row i starts at
+// batch_row_off(i); the HBM layout stays the plain packed triangle.
+__host__ __device__ __forceinline__ int batch_row_off(int i) {
+  const int k = i >> 1;
+  return (i & 1) ? 2 * (k + 1) * (k + 1) : 2 * k * (k + 1);
+}
+// G (n x 2) is kept as two arrays, even columns then odd columns, (n+1)/2 entries each: the two G rows of a
+// 2x2 block are then conflict-free 128-bit loads across the warp.
+__host__ __device__ __forceinline__ int batch_g_idx(int j, int half) { return (j & 1) * half + (j >> 1); }
+
+// Tiled layout (DD = 2): tile (I, J <= I) of 8x8 doubles at (I (I + 1) / 2 + J) * 64.  Inside a tile the unit is the
+// 16-byte chunk a lane holds of the DMMA accumulator (lane l: row l / 4, columns 2 (l % 4), +1).  Row pair h = r / 2
+// keeps its own 128 bytes (so a quarter-warp of the tile load / store still covers all 32 banks), but inside it the
+// chunks are permuted: column chunk ^ f(h), and the two rows swap halves in odd block-rows.  A walk down one COLUMN (the
+// G = Sigma H^T gather, the pose-panel rows of the candidates) then spreads over all eight chunk positions instead of
+// hitting one or two banks.  Diagonal tiles are stored whole; their strictly upper part and rows / columns >= n are
+// padding nobody reads.
+__host__ __device__ __forceinline__ int batch_tile_chunk(int I, int r, int c2) {
+  // f = multiplication by a primitive element of GF(4) (0, 1, 2, 3 -> 0, 2, 3, 1): both h -> f(h) and h -> h ^ f(h)
+  // are bijections, so a column walk AND the diagonal (the candidates' own 2x2 blocks) spread over the chunks
+  const int h = r >> 1, f = (0x78 >> (2 * h)) & 3;
+  return (h << 3) | ((((r ^ I) & 1)) << 2) | (c2 ^ f);
+}
+__host__ __device__ __forceinline__ int batch_tile_idx(int i, int c) {
+  const int I = i >> 3, J = c >> 3;
+  return ((I * (I + 1) / 2 + J) << 6) + (batch_tile_chunk(I, i & 7, (c & 7) >> 1) << 1) + (c & 1);
+}
+// offset of stored element (i, c <= i) / doubles of Sigma storage / entries of the G and K arrays per layout
+template <int DD> __host__ __device__ __forceinline__ int batch_s_idx(int i, int c) {
+  return DD == 2 ? batch_tile_idx(i, c) : batch_row_off(i) + c;
+}
+__host__ __device__ inline int batch_s_doubles(int n, int dd) {
+  const int nt = (n + 7) >> 3;
+  return dd == 2 ? nt * (nt + 1) / 2 * 64 : batch_row_off(n);
+}
+__host__ __device__ inline int batch_gk_entries(int n, int dd) { return dd == 2 ? ((n + 7) & ~7) : 2 * ((n + 1) / 2) + 1; }
+
+__host__ __device__ inline size_t batch_smem_bytes(int n, int m, int dd) {
+  //      Sigma                          mu (even count)         G + K as double2                         polar sightings
+  return ((size_t)batch_s_doubles(n, dd) + (size_t)(n + (n & 1)) + 4 * (size_t)batch_gk_entries(n, dd) + 2 * (size_t)m + 8) *
+         sizeof(double);
 }
 
 // Sigma_0 = diag(0, 0, 0, prior * I_2N) for every filter: slam.cpp:128-132
@@ -57,24 +109,39 @@ __global__ void batch_init_prior_kernel(double *sigma, int B, int n, int tri, do
   if (i >= 3) sigma[(size_t)f * tri + (size_t)i * (i + 1) / 2 + i] = prior;
 }
 
-__device__ __forceinline__ int tri_idx(int i, int j) { return i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i; }
+template <int DD> __device__ __forceinline__ int tri_idx(int i, int j) {
+  return i >= j ? batch_s_idx<DD>(i, j) : batch_s_idx<DD>(j, i);
+}
+__device__ __forceinline__ void dmma884_b(double &c0, double &c1, double a, double b) {   // D = A (8x4) B (4x8) + C
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
 
-__global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchParams p) {
+template <int MINB, bool ONEPASS, int DD>
+__global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const BatchParams p) {
   extern __shared__ __align__(16) double sm[];
   const int n = p.n, tri = p.tri;
-  double *S = sm;                 // packed lower triangle
-  double *mu = S + tri;           // state
-  double2 *G = reinterpret_cast<double2 *>(mu + n + (n & 1));   // G = Sigma H^T   (n x 2)
-  double2 *K = G + n;                                           // K = G S^-1      (n x 2)
-  double *ZP = reinterpret_cast<double *>(K + n);               // polar sightings (m x 2)
+  const int half = (n + 1) >> 1;
+  const int gk = batch_gk_entries(n, DD);
+  double *S = sm;                         // stored triangle: 16-byte aligned rows (DD 0, 1) or 8x8 tiles (DD 2)
+  double *mu = S + batch_s_doubles(n, DD);   // state
+  double2 *G = reinterpret_cast<double2 *>(mu + n + (n & 1));   // G = Sigma H^T   (n x 2); DD 1: even | odd columns
+  double2 *K = G + gk;                                          // K = G S^-1      (n x 2)
+  double *ZP = reinterpret_cast<double *>(K + gk);              // polar sightings (m x 2)
+  auto g_at = [&](int j) { return DD == 1 ? batch_g_idx(j, half) : j; };
   const int f = blockIdx.x;
   const int lane = threadIdx.x;
   if (f >= p.B) return;
 
   // ---- load the filter (coalesced) ---------------------------------------------------------
   {
+    if constexpr (DD == 2) {   // padding of the tiles and the G / K rows beyond n must stay finite zeros
+      for (int e = lane; e < batch_s_doubles(n, DD); e += 32) S[e] = 0.0;
+      for (int e = lane; e < 2 * gk; e += 32) G[e] = make_double2(0.0, 0.0);
+      __syncwarp();
+    }
     const double *gs = p.sigma + (size_t)f * tri;
-    for (int e = lane; e < tri; e += 32) S[e] = gs[e];
+    for (int e = lane; e < tri; e += 32) S[__ldg(p.soff + e)] = gs[e];
     const double *gm = p.mu + (size_t)f * n;
     for (int i = lane; i < n; i += 32) mu[i] = gm[i];
   }
@@ -87,17 +154,18 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
     const double x = p.pose[3 * f + 1], y = p.pose[3 * f + 2];
     const double dx = x - p.prev[2 * f], dy = y - p.prev[2 * f + 1];
     for (int i = 3 + lane; i < n; i += 32) {       // rows >= 3 of the pose panel: C = B A^T
-      const int r = i * (i + 1) / 2;
+      const int r = batch_s_idx<DD>(i, 0);
+      const int r2 = batch_s_idx<DD>(i, 2);
       const double s0 = S[r];
       S[r + 1] = s0 * (-dy) + S[r + 1];
-      S[r + 2] = s0 * dx + S[r + 2];
+      S[r2] = s0 * dx + S[r2];
     }
     if (lane == 0) {
       double P[3][3], Bm[3][3];
 #pragma unroll
       for (int i = 0; i < 3; ++i)
 #pragma unroll
-        for (int j = 0; j <= i; ++j) P[i][j] = P[j][i] = S[i * (i + 1) / 2 + j];
+        for (int j = 0; j <= i; ++j) P[i][j] = P[j][i] = S[batch_s_idx<DD>(i, j)];
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
         Bm[0][j] = P[0][j];
@@ -115,7 +183,7 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
 #pragma unroll
       for (int i = 0; i < 3; ++i)
 #pragma unroll
-        for (int j = 0; j <= i; ++j) S[i * (i + 1) / 2 + j] = P[i][j];
+        for (int j = 0; j <= i; ++j) S[batch_s_idx<DD>(i, j)] = P[i][j];
       mu[0] = th; mu[1] = x; mu[2] = y;
     }
   }
@@ -138,7 +206,7 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
 #pragma unroll
     for (int i = 0; i < 3; ++i)
 #pragma unroll
-      for (int j = 0; j <= i; ++j) pb[i][j] = pb[j][i] = S[i * (i + 1) / 2 + j];
+      for (int j = 0; j <= i; ++j) pb[i][j] = pb[j][i] = S[batch_s_idx<DD>(i, j)];
 
     int j = -1, is_new = 0;
     // linearisation of the landmark being fused: in the matched case it is the winning lane's own
@@ -152,21 +220,32 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
       // quotients (dx/sd, dy/sd, dx/d, dy/d), S^-1 and the innovation
       double r_xs = 0.0, r_ys = 0.0, r_xd = 0.0, r_yd = 0.0, r_m00 = 0.0, r_m01 = 0.0, r_m11 = 0.0, r_z0 = 0.0,
              r_z1 = 0.0;
-      for (int k = lane; k < cnt; k += 32) {                   // slam.cpp:361-404
-        const int a = 3 + 2 * k, ra = a * (a + 1) / 2, rb = (a + 1) * (a + 2) / 2;
-        const double pa[3] = {S[ra], S[ra + 1], S[ra + 2]}, pbr[3] = {S[rb], S[rb + 1], S[rb + 2]};
+      for (int k = lane; k < cnt; k += 32) {                   // slam.cpp:361-404 (ONEPASS: at most one trip)
+        // columns 0, 1 of a row are adjacent in both layouts; everything else is looked up
+        const int a = 3 + 2 * k, ra = batch_s_idx<DD>(a, 0), rb = batch_s_idx<DD>(a + 1, 0);
+        const double pa[3] = {S[ra], S[ra + 1], S[batch_s_idx<DD>(a, 2)]},
+                     pbr[3] = {S[rb], S[rb + 1], S[batch_s_idx<DD>(a + 1, 2)]};
         const Lin Lk = linearize(th, px, py, mu[a], mu[a + 1]);
-        const Block5 Bk = make_block5(pb, pa, pbr, S[ra + a], S[rb + a], S[rb + a + 1]);
+        const Block5 Bk = make_block5(pb, pa, pbr, S[batch_s_idx<DD>(a, a)], S[batch_s_idx<DD>(a + 1, a)],
+                                      S[batch_s_idx<DD>(a + 1, a + 1)]);
         const Innov I = innovation(Bk, Lk, p.r_noise);
         const double z0 = z.r - Lk.zhat_r, z1 = normalize_angle(z.phi - Lk.zhat_b);
         double i00, i01, i11;
         const double d = mahalanobis(I.s00, I.s01, I.s11, z0, z1, i00, i01, i11);
-        const Cand nb = cand_min(best, Cand{d, k});
-        if (nb.k == k) {
+        if constexpr (ONEPASS) {
+          // the only candidate of this lane: a NaN / +inf distance keeps the sentinel, as cand_min would
+          if (d < INFINITY) best = Cand{d, k};
           r_xs = Lk.h0[3]; r_ys = Lk.h0[4]; r_xd = Lk.h1[4]; r_yd = -Lk.h1[3];
           r_m00 = i00; r_m01 = i01; r_m11 = i11; r_z0 = z0; r_z1 = z1;
+          break;
+        } else {
+          const Cand nb = cand_min(best, Cand{d, k});
+          if (nb.k == k) {
+            r_xs = Lk.h0[3]; r_ys = Lk.h0[4]; r_xd = Lk.h1[4]; r_yd = -Lk.h1[3];
+            r_m00 = i00; r_m01 = i01; r_m11 = i11; r_z0 = z0; r_z1 = z1;
+          }
+          best = nb;
         }
-        best = nb;
       }
       best = warp_argmin(best);
       if (best.d <= p.thr && best.k < cnt) {                   // slam.cpp:406-408,418-440
@@ -193,7 +272,7 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
     if (j < 0) continue;                                       // uniform across the warp
 
     // ---- update with landmark j: slam.cpp:443-488 ----------------------------------------------------
-    const int a = 3 + 2 * j, ra = a * (a + 1) / 2, rb = (a + 1) * (a + 2) / 2;
+    const int a = 3 + 2 * j, ra = batch_s_idx<DD>(a, 0), rb = batch_s_idx<DD>(a + 1, 0);
     double lx, ly;
     if (is_new) {                                              // slam.cpp:214-215 / :351-354
       lx = px + z.r * cos(z.phi + th);
@@ -202,8 +281,10 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
     } else { lx = mu[a]; ly = mu[a + 1]; }
     if (!have) {                                               // new landmark / known association
       L = linearize(th, px, py, lx, ly);
-      const double pa[3] = {S[ra], S[ra + 1], S[ra + 2]}, pbr[3] = {S[rb], S[rb + 1], S[rb + 2]};
-      const Block5 Bk = make_block5(pb, pa, pbr, S[ra + a], S[rb + a], S[rb + a + 1]);
+      const double pa[3] = {S[ra], S[ra + 1], S[batch_s_idx<DD>(a, 2)]},
+                   pbr[3] = {S[rb], S[rb + 1], S[batch_s_idx<DD>(a + 1, 2)]};
+      const Block5 Bk = make_block5(pb, pa, pbr, S[batch_s_idx<DD>(a, a)], S[batch_s_idx<DD>(a + 1, a)],
+                                    S[batch_s_idx<DD>(a + 1, a + 1)]);
       const Innov I = innovation(Bk, L, p.r_noise);
       zd0 = z.r - L.zhat_r; zd1 = normalize_angle(z.phi - L.zhat_b);
       (void)mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, m00, m01, m11);
@@ -212,12 +293,12 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
     if (is_new && lane == 0) { mu[a] = lx; mu[a + 1] = ly; }
     __syncwarp();
     for (int i = lane; i < n; i += 32) {                       // G = Sigma H^T, K = G S^-1, state
-      const double row[5] = {S[tri_idx(i, 0)], S[tri_idx(i, 1)], S[tri_idx(i, 2)], S[tri_idx(i, a)],
-                             S[tri_idx(i, a + 1)]};
+      const double row[5] = {S[tri_idx<DD>(i, 0)], S[tri_idx<DD>(i, 1)], S[tri_idx<DD>(i, 2)], S[tri_idx<DD>(i, a)],
+                             S[tri_idx<DD>(i, a + 1)]};
       double g0, g1;
       row_times_ht(row, L, g0, g1);
       const double k0 = g0 * m00 + g1 * m01, k1 = g0 * m01 + g1 * m11;
-      G[i] = make_double2(g0, g1);
+      G[g_at(i)] = make_double2(g0, g1);
       K[i] = make_double2(k0, k1);
       double v = mu[i] + (k0 * zd0 + k1 * zd1);                // slam.cpp:482
       if (i == 0) v = normalize_angle(v);                      // slam.cpp:488
@@ -227,10 +308,49 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
     // Sigma -= K G^T on the stored triangle, element by element in packed order: 32 consecutive
     // elements per step keep every lane busy (a column-per-lane walk idles half of them on the triangle);
     // (row, column) of an element comes from a small table that stays in L1
-    for (int e = lane; e < tri; e += 32) {
-      const uchar2 ic = __ldg(p.tri_map + e);
-      const double2 ki = K[ic.x], gc = G[ic.y];
-      S[e] = S[e] - (ki.x * gc.x + ki.y * gc.y);
+    if constexpr (DD == 2) {
+      // C tile (accumulator order in shared memory) += (-K rows of block-row I) x (G rows of block-column J)^T;
+      // fragment element (row lane / 4, k = lane % 4): k = 0, 1 are the two columns of K / G, k = 2, 3 are zero
+      const int nt = (n + 7) >> 3, fr = lane >> 2, fk = lane & 3;
+      const double *Kd = reinterpret_cast<const double *>(K), *Gd = reinterpret_cast<const double *>(G);
+      const double2 *tile = reinterpret_cast<const double2 *>(S);
+      const int ch[2] = {batch_tile_chunk(0, fr, fk), batch_tile_chunk(1, fr, fk)};   // this lane's chunk, even / odd I
+      for (int I = 0; I < nt; ++I) {
+        const double aI = fk < 2 ? -Kd[(8 * I + fr) * 2 + fk] : 0.0;
+        double2 *ct = const_cast<double2 *>(tile) + ch[I & 1];
+        for (int J = 0; J <= I; ++J, ct += 32) {
+          const double bJ = fk < 2 ? Gd[(8 * J + fr) * 2 + fk] : 0.0;
+          double2 c = *ct;
+          dmma884_b(c.x, c.y, aI, bJ);
+          *ct = c;
+        }
+        tile += 32 * (I + 1);
+      }
+    } else if constexpr (DD == 1) {
+      // 2x2 blocks: two K rows and two G columns serve up to four elements.  K[n] / G[n] of an odd n are read
+      // (they alias the next array) but their products are masked out.
+      for (int q = lane; q < p.nblk; q += 32) {
+        const ushort4 bm = __ldg(p.blk_map + q);
+        const double2 ka = K[bm.x], kb = K[bm.x + 1], ga = G[bm.y >> 1], gb = G[half + (bm.y >> 1)];
+        // rows i0 (even) and i0 + 1 are the same padded length: the block's second row is i0 + 2 doubles on
+        double2 *s0 = reinterpret_cast<double2 *>(S + bm.z), *s1 = reinterpret_cast<double2 *>(S + bm.z + bm.x + 2);
+        double2 a0 = *s0, a1 = *s1;
+        a0.x = a0.x - (ka.x * ga.x + ka.y * ga.y);
+        a0.y = a0.y - (ka.x * gb.x + ka.y * gb.y);
+        a1.x = a1.x - (kb.x * ga.x + kb.y * ga.y);
+        a1.y = a1.y - (kb.x * gb.x + kb.y * gb.y);
+        // elements outside the stored triangle ((i0, i0+1) on the diagonal, row n of an odd n) are padding:
+        // written with whatever the arithmetic gave, never read by anything else
+        *s0 = a0;
+        if (bm.w & 4) *s1 = a1;
+      }
+    } else {
+      for (int e = lane; e < tri; e += 32) {
+        const uchar2 ic = __ldg(p.tri_map + e);
+        const double2 ki = K[ic.x], gc = G[ic.y];
+        const int o = batch_row_off(ic.x) + ic.y;
+        S[o] = S[o] - (ki.x * gc.x + ki.y * gc.y);
+      }
     }
     __syncwarp();
   }
@@ -238,7 +358,7 @@ __global__ void __launch_bounds__(kBatchThreads) ekf_batch_kernel(const BatchPar
   // ---- store back ----------------------------------------------------------------------------------
   {
     double *gs = p.sigma + (size_t)f * tri;
-    for (int e = lane; e < tri; e += 32) gs[e] = S[e];
+    for (int e = lane; e < tri; e += 32) gs[e] = S[__ldg(p.soff + e)];
     double *gm = p.mu + (size_t)f * n;
     for (int i = lane; i < n; i += 32) gm[i] = mu[i];
     if (lane == 0) {
