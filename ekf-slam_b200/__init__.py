@@ -64,6 +64,7 @@ def load() -> C.CDLL:
         "ekf_default_config": (None, [C.POINTER(EkfConfig)]),
         "ekf_status_string": (C.c_char_p, [C.c_int]),
         "ekf_version": (C.c_char_p, []),
+        "ekf_selftest_division": (C.c_int, [i32, C.c_uint64, i32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
         "ekf_create": (C.c_int, [C.POINTER(EkfConfig), C.POINTER(vp)]),
         "ekf_destroy": (C.c_int, [vp]),
         "ekf_set_stream": (C.c_int, [vp, vp]),
@@ -136,6 +137,15 @@ def load() -> C.CDLL:
 
 def status_string(status: int) -> str:
     return load().ekf_status_string(int(status)).decode()
+
+
+def selftest_division(count: int = 1 << 22, seed: int = 1, device: int = -1):
+    """(mismatches, outside_guard) of the kernels' shared-reciprocal division against IEEE `/` on the device."""
+    mis, slow = C.c_uint64(0), C.c_uint64(0)
+    st = load().ekf_selftest_division(device, seed, count, C.byref(mis), C.byref(slow))
+    if st != 0:
+        raise RuntimeError(f"ekf_selftest_division: {status_string(st)}")
+    return int(mis.value), int(slow.value)
 
 
 def _dp(a):

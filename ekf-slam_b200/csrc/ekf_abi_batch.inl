@@ -21,7 +21,7 @@ struct ekf_batch {
 
 namespace {
 
-constexpr int BATCH_DEFAULT_VARIANT = 13;   // 20 CTAs/SM, one-pass association, 2x2-block downdate (measured best)
+constexpr int BATCH_DEFAULT_VARIANT = 6;   // one-pass association + DMMA 8x8-tile downdate, 16 CTAs/SM (measured best)
 
 #define CKB(b, call)                                                               \
   do {                                                                             \

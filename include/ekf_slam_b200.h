@@ -69,6 +69,12 @@ typedef struct ekf_nusim ekf_nusim;         /* nusim's sensor models as device-s
 void ekf_default_config(ekf_config *cfg);
 const char *ekf_status_string(int status);
 const char *ekf_version(void);
+/* Device self-test of the shared-reciprocal fp64 division the kernels use for the reference's quotients
+ * (slam.cpp:234-249 Jacobian entries, the 2x2 inverse behind :401 / :476): `count` hashed operand pairs (all
+ * exponents, specials, and the filter's own magnitudes) are divided both ways on device `device` (-1: current).
+ * *mismatches = pairs inside the fast path's guard whose quotient differs in any bit from IEEE `a / b` (must be 0);
+ * *outside_guard = pairs the guard sends to the plain division. */
+int ekf_selftest_division(int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard);
 
 /* ---- lifetime: replaces slam.cpp:127-139 ------------------------------------------------ */
 int ekf_create(const ekf_config *cfg, ekf_filter **out);

@@ -309,3 +309,13 @@ def test_maximum_size_N60k_properties():
     assert cnt2 == count + 4 and (np.asarray(a2) >= 0).all()
     assert g.last_status() == 0
     g.close()
+
+
+def test_shared_reciprocal_division_is_ieee_division():
+    """The kernels form the reference's quotients (slam.cpp:234-249, the 2x2 inverse of :401/:476) with a
+    shared-reciprocal sequence instead of `/`: on the device it must give the IEEE quotient bit for bit
+    wherever its guard admits the operands (everything else goes through `/` itself)."""
+    for seed in (1, 2, 3):
+        mismatches, outside = ekf_slam_b200.selftest_division(count=1 << 22, seed=seed)
+        assert mismatches == 0
+        assert outside < (1 << 22)          # the fast path is actually taken
