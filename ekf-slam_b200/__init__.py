@@ -64,6 +64,13 @@ def load() -> C.CDLL:
         "ekf_default_config": (None, [C.POINTER(EkfConfig)]),
         "ekf_status_string": (C.c_char_p, [C.c_int]),
         "ekf_version": (C.c_char_p, []),
+        "ekf_bag_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(vp)]),
+        "ekf_bag_close": (C.c_int, [vp]),
+        "ekf_bag_last_error": (C.c_char_p, []),
+        "ekf_bag_counts": (C.c_int, [vp, i64p, i64p, i64p, i64p, i64p]),
+        "ekf_bag_event": (C.c_int, [vp, C.c_int64, ip, ip, C.POINTER(C.c_uint64)]),
+        "ekf_bag_joint_state": (C.c_int, [vp, i32, i64p, ip, i32, dp]),
+        "ekf_bag_detections": (C.c_int, [vp, i32, ip, i32, dp, ip, ip]),
         "ekf_selftest_division": (C.c_int, [i32, C.c_uint64, i32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
         "ekf_create": (C.c_int, [C.POINTER(EkfConfig), C.POINTER(vp)]),
         "ekf_destroy": (C.c_int, [vp]),

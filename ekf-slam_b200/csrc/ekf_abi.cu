@@ -178,3 +178,4 @@ int env_int(const char *name, int dflt) {
 #include "ekf_abi_shard.inl"
 #include "ekf_abi_landmarks.inl"
 #include "ekf_abi_nusim.inl"
+#include "ekf_abi_bag.inl"

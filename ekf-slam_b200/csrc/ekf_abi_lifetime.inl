@@ -26,6 +26,7 @@ const char *ekf_status_string(int status) {
     case EKF_ERR_CUDA: return "CUDA error";
     case EKF_ERR_NO_DEVICE: return "no usable CUDA device";
     case EKF_ERR_NOMEM: return "out of memory";
+    case EKF_ERR_IO: return "bag file unreadable or unsupported";
     default: return "unknown status";
   }
 }

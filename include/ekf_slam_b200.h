@@ -40,7 +40,8 @@ typedef enum ekf_status {
   EKF_ERR_BAD_ID = 4,     /* known-association id outside [0, N) (Armadillo bounds error) */
   EKF_ERR_CUDA = 5,       /* a CUDA call failed; see ekf_last_cuda_error */
   EKF_ERR_NO_DEVICE = 6,  /* no usable sm_100 device */
-  EKF_ERR_NOMEM = 7
+  EKF_ERR_NOMEM = 7,
+  EKF_ERR_IO = 8          /* bag file unreadable / not MCAP / unsupported encoding; see ekf_bag_last_error */
 } ekf_status;
 
 /* Filter constants.  Defaults (ekf_default_config) are the reference's hard-coded members:
@@ -278,6 +279,33 @@ int ekf_nusim_lidar(ekf_nusim *h, int32_t n_robots, const double *poses, double 
                     uint64_t seed, const double *noise, float *out_ranges);
 int ekf_nusim_lidar_dev(ekf_nusim *h, int32_t n_robots, const double *poses_dev, double max_range, double noise_std,
                         uint64_t seed, const double *noise_dev, float *out_ranges_dev, void *cuda_stream);
+
+/* ---- N4: rosbag2 (MCAP container, CDR payload) reader for the node's two input topics -------------------------
+ * Replaces, for offline replay, what rclcpp + rosbag2 deliver to Slam::jointStateCallback (slam.cpp:599-634,
+ * sensor_msgs/msg/JointState on `joint_states`) and Slam::sensor_cb / fake_sensor_cb (slam.cpp:318, :180,
+ * visualization_msgs/msg/MarkerArray on `green/detected_obstacles` / `nusim/fake_sensor`); topic names default to
+ * the recorded ones of rosbags/rosbag2_2024_03_17-18_35_57/metadata.yaml:116-121,158-163.  Host-only (no GPU).
+ * The whole file is parsed at open; events are the two topics merged in MCAP log-time order (ties: joint state
+ * first), i.e. the order the node's single-threaded executor (slam.cpp:680-686) would have seen them. */
+typedef struct ekf_bag ekf_bag;
+/* joint_topic / detections_topic: NULL = "/blue/joint_states" / "/green/detected_obstacles" */
+int ekf_bag_open(const char *path, const char *joint_topic, const char *detections_topic, ekf_bag **out);
+int ekf_bag_close(ekf_bag *b);
+/* message of the last failed ekf_bag_open on this thread ("" if none) */
+const char *ekf_bag_last_error(void);
+/* counts: events, joint states, detection arrays, all messages in the file (any topic), chunks */
+int ekf_bag_counts(const ekf_bag *b, int64_t *events, int64_t *joint_states, int64_t *detection_arrays,
+                   int64_t *messages_total, int64_t *chunks);
+/* event e: kind 0 = joint state, 1 = detection array; index into that kind's list; MCAP log time (ns) */
+int ekf_bag_event(const ekf_bag *b, int64_t e, int32_t *kind, int32_t *index, uint64_t *log_time_ns);
+/* joint state i: header stamp (ns), number of joints, and the first min(cap, n) positions (the callback reads
+ * position[0] = left and position[1] = right wheel, slam.cpp:604) */
+int ekf_bag_joint_state(const ekf_bag *b, int32_t i, int64_t *stamp_ns, int32_t *n_joints, int32_t cap,
+                        double *positions);
+/* detection array i: number of markers and, for the first min(cap, n): pose.position (x, y) pairs, marker.id,
+ * marker.action (ADD 0 / DELETE 2) - the fields slam.cpp:203-210 / :340-347 read */
+int ekf_bag_detections(const ekf_bag *b, int32_t i, int32_t *n_markers, int32_t cap, double *xy, int32_t *ids,
+                       int32_t *actions);
 
 #ifdef __cplusplus
 }

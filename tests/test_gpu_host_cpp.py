@@ -48,3 +48,34 @@ def test_slam_core_replay_matches_oracle_a(tmp_path, known):
         got = [[int(v) for v in r.split()[4:]] for r in rows[:len(scans)]]
         assert got == [list(map(int, a)) for a in aL]
     assert rows[-1].startswith("MAPODOM")
+
+
+def test_replay_bag_program_matches_oracle_a(tmp_path):
+    """tools/replay_bag.cpp: MCAP file -> rosbag::McapReader -> nuslam::SlamCore (C++ end to end, SURVEY 8f N3 + N4)
+    against oracle A fed the same wheel angles and sightings."""
+    import _mcap_writer as mw
+    pkg = os.path.join(ROOT, "ekf-slam_b200")
+    exe = str(tmp_path / "replay_bag")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-pedantic", "-ffp-contract=off",
+                           "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(pkg, "host"),
+                           os.path.join(ROOT, "tools", "replay_bag.cpp"), "-o", exe,
+                           "-L" + pkg, "-lekf_slam_b200", "-Wl,-rpath," + pkg, "-ldl"])
+    scans = [s for s in synth.circle_drive(n_scans=60, seed=22, drop_out_of_range=True, shuffle=True) if len(s.xy)]
+    channels = {1: ("/blue/joint_states", "sensor_msgs/msg/JointState"),
+                2: ("/green/detected_obstacles", "visualization_msgs/msg/MarkerArray")}
+    msgs, t = [], 1710718557269449803
+    for s in scans:
+        t += 200_000_000
+        msgs.append((1, t, mw.encode_joint_state(t, ["wheel_left_joint", "wheel_right_joint"], s.wheels)))
+        msgs.append((2, t + 1000, mw.encode_marker_array(t, [{"id": int(i), "x": float(x), "y": float(y)}
+                                                             for i, (x, y) in zip(s.ids, s.xy)])))
+    path = str(tmp_path / "bag_0.mcap")
+    mw.write_mcap(path, channels, msgs, chunk_messages=16)
+    out = subprocess.run([exe, path], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    rows = out.stdout.strip().split("\n")
+    aL, sL, _, cL = run_literal(scans, False)
+    assert len(rows) == len(scans) + 1 and rows[-1].startswith("MAPODOM")
+    assert [[int(v) for v in r.split()[5:]] for r in rows[:-1]] == [list(map(int, a)) for a in aL]
+    last = rows[-2].split()
+    assert np.allclose([float(v) for v in last[1:4]], sL[:3], rtol=0, atol=1e-9) and int(last[4]) == cL
