@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
       __syncwarp();
     }
     const double *gs = p.sigma + (size_t)f * tri;
+#pragma unroll 4
     for (int e = lane; e < tri; e += 32) S[__ldg(p.soff + e)] = gs[e];
     const double *gm = p.mu + (size_t)f * n;
     for (int i = lane; i < n; i += 32) mu[i] = gm[i];
@@ -358,6 +359,7 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
   // ---- store back ----------------------------------------------------------------------------------
   {
     double *gs = p.sigma + (size_t)f * tri;
+#pragma unroll 4
     for (int e = lane; e < tri; e += 32) gs[e] = S[__ldg(p.soff + e)];
     double *gm = p.mu + (size_t)f * n;
     for (int i = lane; i < n; i += 32) gm[i] = mu[i];
