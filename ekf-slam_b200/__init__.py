@@ -75,6 +75,7 @@ def load() -> C.CDLL:
         "ekf_create": (C.c_int, [C.POINTER(EkfConfig), C.POINTER(vp)]),
         "ekf_destroy": (C.c_int, [vp]),
         "ekf_set_stream": (C.c_int, [vp, vp]),
+        "ekf_set_overlap": (C.c_int, [vp, i32]),
         "ekf_synchronize": (C.c_int, [vp]),
         "ekf_last_status": (C.c_int, [vp]),
         "ekf_last_cuda_error": (C.c_char_p, [vp]),
@@ -211,6 +212,15 @@ class EkfSlam:
 
     def set_stream(self, cuda_stream_ptr: int):
         self._check(self._L.ekf_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "ekf_set_stream")
+
+    def set_overlap(self, on: bool = True) -> bool:
+        """Overlap the covariance pass of a scan with the sequential side of the next one (ekf_set_overlap).
+        Returns False (and stays on the classic path) when the second covariance buffer does not fit."""
+        rc = self._L.ekf_set_overlap(self._h, 1 if on else 0)
+        if rc == 7:          # EKF_ERR_NOMEM
+            return False
+        self._check(rc, "ekf_set_overlap")
+        return bool(on)
 
     def synchronize(self):
         self._check(self._L.ekf_synchronize(self._h), "ekf_synchronize")

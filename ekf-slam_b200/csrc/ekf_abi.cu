@@ -85,6 +85,19 @@ struct ekf_filter {
   int dd_variant = 2;      // 0: <64 rows, register prefetch>, 1 CTA / SM;  1: <32 rows>, 3 CTAs / SM
   int latched = EKF_OK;
   std::string cuda_err;
+  // overlapped scans (ekf_set_overlap, ekf_abi_overlap.inl): the covariance pass of scan s runs out of place on a
+  // second stream while the sequential side of scan s+1 runs on `stream`
+  bool overlap = false;          // requested
+  bool pipe_active = false;      // rounds issued since the last drain
+  double *sigma2 = nullptr;      // the other covariance buffer (pass k reads buffer k & 1, writes the other)
+  double *W2 = nullptr, *V2 = nullptr;   // the other panel pair (round k writes / pass k reads pair k & 1)
+  cudaStream_t back_stream = nullptr;
+  cudaEvent_t ev_seq[2] = {nullptr, nullptr}, ev_pass[2] = {nullptr, nullptr};
+  int64_t pipe_step = 0;         // rounds issued since the pipeline was entered
+  int pipe_k2_prev = 0;          // panel columns of the previous round's pass
+  int pipe_grid = 1;             // CTAs of the sequential kernel that fit beside the pass (<= one per SM)
+  int *done_host = nullptr;      // pinned: measurements the last round processed
+  cudaEvent_t done_event = nullptr;
 };
 
 namespace {
@@ -171,6 +184,7 @@ int env_int(const char *name, int dflt) {
 
 }  // namespace
 
+#include "ekf_abi_overlap.inl"
 #include "ekf_abi_lifetime.inl"
 #include "ekf_abi_scan.inl"
 #include "ekf_abi_access.inl"

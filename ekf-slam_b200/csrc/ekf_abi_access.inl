@@ -98,6 +98,7 @@ int ekf_get_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
   if (!block_args_ok(f, i0, i1, j0, j1, out)) return EKF_ERR_INVALID;
   if (i1 == i0 || j1 == j0) return EKF_OK;
   DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
   const size_t ld = (size_t)(j1 - j0);
   size_t rows_per = kBlockPieceBytes / (ld * 8);
   if (rows_per < 1) rows_per = 1;
@@ -120,6 +121,7 @@ int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
   if (i1 == i0 || j1 == j0) return EKF_OK;
   f->side_valid = false;
   DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
   const size_t ld = (size_t)(j1 - j0);
   size_t rows_per = kBlockPieceBytes / (ld * 8);
   if (rows_per < 1) rows_per = 1;
@@ -141,6 +143,7 @@ int ekf_fill_procedural(ekf_filter *f, uint64_t seed, int32_t count, int32_t gri
   if (!f || count < 0 || count > f->N || grid_w < 1) return EKF_ERR_INVALID;
   f->side_valid = false;
   DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
   fill_procedural_sigma_kernel<<<f->num_sms * 16, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, count, seed, f->cfg.prior);
   fill_procedural_state_kernel<<<(f->N + 255) / 256, 256, 0, f->stream>>>(f->mu, f->n_pad, f->N, count, grid_w, seed);
   f->launches += 2;

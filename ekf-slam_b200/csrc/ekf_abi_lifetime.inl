@@ -60,6 +60,7 @@ int ekf_destroy(ekf_filter *f) {
   {
     DeviceGuard guard(f->device);
     if (f->stream) cudaStreamSynchronize(f->stream);
+    pipe_release(f);
     cudaFree(f->sigma); cudaFree(f->mu); cudaFree(f->W); cudaFree(f->V);
     cudaFree(f->Pp); cudaFree(f->cnt); cudaFree(f->status);   // D lives in the Pp allocation
     cudaFree(f->cols); cudaFree(f->guess); cudaFree(f->done_dev);
@@ -217,6 +218,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
 int ekf_set_stream(ekf_filter *f, void *cuda_stream) {
   if (!f) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
   CK(f, cudaStreamSynchronize(f->stream));
   f->stream = cuda_stream ? (cudaStream_t)cuda_stream : f->own_stream;
   return EKF_OK;
@@ -225,6 +227,7 @@ int ekf_set_stream(ekf_filter *f, void *cuda_stream) {
 int ekf_synchronize(ekf_filter *f) {
   if (!f) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
+  if (f->back_stream) CK(f, cudaStreamSynchronize(f->back_stream));   // a pass of the overlapped mode (no drain)
   CK(f, cudaStreamSynchronize(f->stream));
   return EKF_OK;
 }
@@ -248,8 +251,9 @@ int ekf_enable_timing(ekf_filter *f, int32_t ring_scans) {
   if (!f || ring_scans < 0) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
   CK(f, cudaStreamSynchronize(f->stream));
+  if (f->back_stream) CK(f, cudaStreamSynchronize(f->back_stream));
   for (auto &e : f->ev) if (e) cudaEventDestroy(e);
-  f->ev.assign((size_t)ring_scans * 3, nullptr);
+  f->ev.assign((size_t)ring_scans * 4, nullptr);   // sequential start / end, pass start / end
   for (auto &e : f->ev) CK(f, cudaEventCreate(&e));
   f->ev_cap = ring_scans;
   f->ev_count = 0;
@@ -260,19 +264,36 @@ int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t ma
   if (!f || max_scans < 0) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
   CK(f, cudaStreamSynchronize(f->stream));
+  if (f->back_stream) CK(f, cudaStreamSynchronize(f->back_stream));
   int64_t have = f->ev_count < f->ev_cap ? f->ev_count : f->ev_cap;
   if (have > max_scans) have = max_scans;
   // the most recent `have` scans, oldest first
   for (int64_t i = 0; i < have; ++i) {
     const int64_t scan = f->ev_count - have + i;
-    const size_t slot = (size_t)(scan % f->ev_cap) * 3;
+    const size_t slot = (size_t)(scan % f->ev_cap) * 4;
     float a = 0.f, b = 0.f;
     CK(f, cudaEventElapsedTime(&a, f->ev[slot], f->ev[slot + 1]));
-    CK(f, cudaEventElapsedTime(&b, f->ev[slot + 1], f->ev[slot + 2]));
+    CK(f, cudaEventElapsedTime(&b, f->ev[slot + 2], f->ev[slot + 3]));
     if (seq_ms) seq_ms[i] = a;
     if (downdate_ms) downdate_ms[i] = b;
   }
   if (n_scans) *n_scans = (int32_t)have;
+  return EKF_OK;
+}
+
+int ekf_set_overlap(ekf_filter *f, int32_t on) {
+  if (!f) return EKF_ERR_INVALID;
+  if (f->sharded) return EKF_ERR_INVALID;               // a row shard already overlaps across ranks
+  DeviceGuard guard(f->device);
+  if (!on) {
+    const int rcd = pipe_drain(f);
+    if (rcd != EKF_OK) return rcd;
+    f->overlap = false;
+    return EKF_OK;
+  }
+  const int rc = pipe_resources(f);                     // second covariance buffer: EKF_ERR_NOMEM if it does not fit
+  if (rc != EKF_OK) return rc;
+  f->overlap = true;
   return EKF_OK;
 }
 

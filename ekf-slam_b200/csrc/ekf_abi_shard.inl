@@ -5,19 +5,6 @@ namespace {
 // the shard protocol also runs on an unsharded handle (one shard that owns every row)
 int shard_ok(ekf_filter *f) { return f != nullptr; }
 
-int shard_buffers(ekf_filter *f) {
-  if (!f->cols) CK(f, cudaMalloc(&f->cols, (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double)));
-  if (!f->guess) CK(f, cudaMalloc(&f->guess, kMaxChunkM * sizeof(int)));
-  if (!f->done_dev) CK(f, cudaMalloc(&f->done_dev, sizeof(int)));
-  if (!f->guess_part_d) {
-    CK(f, cudaMalloc(&f->guess_part_d, (size_t)kMaxChunkM * kGuessMaxSlices * sizeof(double)));
-    CK(f, cudaMalloc(&f->guess_part_k, (size_t)kMaxChunkM * kGuessMaxSlices * sizeof(int)));
-    CK(f, cudaMalloc(&f->guess_ticket, kMaxChunkM * sizeof(unsigned int)));
-    CK(f, cudaMemsetAsync(f->guess_ticket, 0, kMaxChunkM * sizeof(unsigned int), f->stream));
-  }
-  return EKF_OK;
-}
-
 // the peer-visible exchange region: two column buffers (round parity) + the arrival flags
 int shard_xchg_region(ekf_filter *f) {
   if (f->xchg) return EKF_OK;
@@ -86,6 +73,7 @@ int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t 
 int ekf_shard_sync_begin(ekf_filter *f, double **xchg_dev, int64_t *xchg_doubles) {
   if (!shard_ok(f) || !xchg_dev || !xchg_doubles) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
   int rcb = shard_buffers(f);
   if (rcb != EKF_OK) return rcb;
   shard_side_extract_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
@@ -111,6 +99,7 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
   if (!shard_ok(f) || m < 1 || !xy_dev || !xchg_dev || !xchg_doubles) return EKF_ERR_INVALID;
   if (!f->side_valid) return EKF_ERR_INVALID;        // ekf_shard_sync_begin / _finish first
   DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
   const int mc = m < kMaxChunkM ? m : kMaxChunkM;    // a round handles at most kMaxChunkM sightings
   if (pose_dev) {
     shard_predict_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->Pp, f->mu, pose_dev, f->prev_xy, f->N,
@@ -195,7 +184,7 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   f->pend_m = -1;
 
   const bool timed = f->ev_cap > 0;
-  const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 3 : 0;
+  const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 4 : 0;
   if (timed) CK(f, cudaEventRecord(f->ev[slot], f->stream));
   void *args[] = {(void *)&sp};
   const void *seq_fn = f->seq_threads == kSeqThreadsSmall ? (const void *)ekf_seq_kernel<kSeqThreadsSmall>
@@ -203,7 +192,7 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
                                     seq_smem_bytes(f->seq_threads), f->stream));
   f->launches++;
-  if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
+  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 1], f->stream)); CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); }
   // association / done / pose / count are final here: hand them to the host before the covariance pass
   if (results_bytes > 0)
     CK(f, cudaMemcpyAsync(results_host, results_dev, (size_t)results_bytes, cudaMemcpyDeviceToHost, f->stream));
@@ -220,7 +209,7 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
   f->launches += 2;
   CK(f, cudaGetLastError());
-  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); f->ev_count++; }
+  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 3], f->stream)); f->ev_count++; }
   return EKF_OK;
 }
 

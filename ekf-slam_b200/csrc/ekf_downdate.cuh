@@ -46,6 +46,7 @@ constexpr int kDdWBufs = 2;   // W rows of the current strip + the next one (loa
 constexpr int dd_threads(int chunk_rows) { return (chunk_rows / 8) * 32 + 32; }
 
 struct DdParams {
+  double *sigma_out;   // nullptr: in place; else the updated triangle goes here (same layout), `sigma` stays intact
   double *sigma;
   const double *V;   // row operand  (K panels)
   const double *W;   // column operand (G panels)
@@ -268,7 +269,7 @@ __global__ void __launch_bounds__(dd_threads(CR), PF ? (CR == 32 ? 2 : 1) : 3) e
   const int ksteps = k2 >> 2;
   for (int it = 0; it < n_chunks; ++it) {
     const int s = it % kDdVStages;
-    double *out = p.sigma + cur.off;
+    double *out = (p.sigma_out ? p.sigma_out : p.sigma) + cur.off;
     const int curJ = cur.J;
     dd_advance(cur, CR, p.lay);
     if (PF == 1) {

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double
     pb[i][0] = r.x; pb[i][1] = r.y; pb[i][2] = r.z;
   }
   Cand best{INFINITY, 0x7fffffff};
-  for (int k = slice * kGuessThreads + threadIdx.x; k < cnt; k += P * kGuessThreads) {
+  for (int k = slice * (int)blockDim.x + threadIdx.x; k < cnt; k += P * (int)blockDim.x) {   // blockDim <= kGuessThreads
     const int a = 4 + 2 * k;
     const double2 lm = *reinterpret_cast<const double2 *>(mu + a);
     const double4 pa = Pp[a], pbr = Pp[a + 1], dk = D[k];
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double
   __syncthreads();
   if (threadIdx.x == 0) {
     Cand c = s_red[0];
-    for (int w = 1; w < kGuessThreads / 32; ++w) c = cand_min(c, s_red[w]);
+    for (int w = 1; w < (int)blockDim.x / 32; ++w) c = cand_min(c, s_red[w]);
     part_d[t * kGuessMaxSlices + slice] = c.d;
     part_k[t * kGuessMaxSlices + slice] = c.k;
     __threadfence();
@@ -160,6 +160,42 @@ __global__ void shard_extract_cols_kernel(const double *sigma, EkfLay lay, int n
         if (ekf_lay_owns_row(lay, a)) {
           v.x = sigma[ekf_lay_elem(lay, a, i)];
           v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
+        }
+      }
+    }
+    *reinterpret_cast<double2 *>(cols + e * 2) = v;
+  }
+}
+
+// ---- overlapped scans on one GPU (ekf_set_overlap): the columns of the covariance the PENDING pass will produce ---
+// While the covariance pass of scan s is still streaming Sigma_old -> Sigma_new (out of place), scan s+1 already
+// needs the raw columns of Sigma_new for its guessed landmarks.  They are formed here from the pass's INPUT and its
+// panels:  Sigma_new[r, c] = Sigma_old[r, c] - sum_q V[r][q] W[c][q]  for the stored (row r >= column c) element,
+// exactly the element the pass writes (it sums the same products on the tensor path, so the two agree to rounding).
+// k2 = 0: no pass pending, plain extraction.  Same output layout as shard_extract_cols_kernel (whole matrix owned).
+__global__ void pipe_extract_cols_kernel(const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m,
+                                         const double *V, const double *W, int kmax, int k2, double *cols) {
+  const int64_t total = (int64_t)m * n_pad;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int slot = (int)(e / n_pad), i = (int)(e % n_pad);
+    const int j = guess[slot];
+    double2 v = make_double2(0.0, 0.0);
+    if (j >= 0 && j < N) {
+      const int a = 4 + 2 * j;
+      if (i > a + 1) {                 // stored elements (i, a), (i, a + 1): V row i, W rows a / a + 1
+        v = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a));
+        for (int q = 0; q < k2; ++q) {
+          const double vi = V[ekf_panel_elem(kmax, i, q)];
+          v.x -= vi * __ldg(W + ekf_panel_elem(kmax, a, q));
+          v.y -= vi * __ldg(W + ekf_panel_elem(kmax, a + 1, q));
+        }
+      } else if (i < a) {              // stored elements (a, i), (a + 1, i): V rows a / a + 1, W row i
+        v.x = sigma[ekf_lay_elem(lay, a, i)];
+        v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
+        for (int q = 0; q < k2; ++q) {
+          const double wi = W[ekf_panel_elem(kmax, i, q)];
+          v.x -= __ldg(V + ekf_panel_elem(kmax, a, q)) * wi;
+          v.y -= __ldg(V + ekf_panel_elem(kmax, a + 1, q)) * wi;
         }
       }
     }

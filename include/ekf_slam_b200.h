@@ -149,6 +149,15 @@ int ekf_fill_procedural(ekf_filter *f, uint64_t seed, int32_t count, int32_t gri
 int ekf_sigma_storage(ekf_filter *f, int64_t *stored_doubles, int64_t *n_pad);
 /* number of kernels this handle has launched since creation */
 int ekf_launch_count(ekf_filter *f, int64_t *launches);
+/* Overlapped scans (single GPU, unsharded handle).  on = 1: from the next ekf_scan / ekf_scan_dev the covariance pass
+ * of a scan (slam.cpp:264-265 / :485-486, deferred, one pass per scan) runs OUT OF PLACE on a second stream while
+ * the prediction, association and state updates of the following scan (slam.cpp:323-482) already run: the two use
+ * disjoint parts of an SM.  Costs a second covariance buffer (returns EKF_ERR_NOMEM and stays off when it does not
+ * fit).  Results are the same filter (the columns the next scan needs are formed as "input of the pending pass
+ * minus its update", which equals what the pass stores up to rounding).  Every accessor, fixture, classic-path call
+ * (ekf_predict / ekf_update_*, scans with an `action` array) and ekf_set_overlap(f, 0) first drains the pipeline.
+ * ekf_synchronize waits for the pending pass as well. */
+int ekf_set_overlap(ekf_filter *f, int32_t on);
 /* Per-scan device timing with CUDA events on the handle's stream.  ekf_enable_timing(f, r)
  * keeps the last r scans (r = 0 switches it off); ekf_read_timing synchronises and returns, for
  * the most recent scans (oldest first), the milliseconds of the sequential phase and of the

@@ -73,14 +73,22 @@ def run_model(scans, known, n_landmarks=50, **kw):
     return assoc, f.mu.copy(), f.sigma(), f.cnt
 
 
-def run_gpu(scans, known, n_landmarks=50, fused=False, **kw):
+def run_gpu(scans, known, n_landmarks=50, fused=False, overlap=False, no_action=False, probe=None, **kw):
+    """overlap: ekf_set_overlap(1) (covariance pass of a scan behind the next scan's sequential side; fused scans
+    only).  no_action: known association without the per-sighting action array (the overlapped path takes ids but
+    not actions).  probe(f, scan_index): called between scans (accessor traffic in the middle of the pipeline)."""
     f = ekf_slam_b200.EkfSlam(n_landmarks=n_landmarks, **kw)
+    if overlap:
+        assert f.set_overlap(True)
     host = synth.MapHost()
     assoc = []
     for s in scans:
         x, y, th = host.composed(s.odom)
+        if probe is not None:
+            probe(f, len(assoc))
         if fused:
-            a, _, pose = f.scan((th, x, y), s.xy, s.ids if known else None, s.action if known else None)
+            a, _, pose = f.scan((th, x, y), s.xy, s.ids if known else None,
+                                s.action if (known and not no_action) else None)
             assoc.append(list(s.ids) if known else list(a))
         else:
             f.predict(th, x, y)
