@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=7)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched-filters section")
+    ap.add_argument("--overlap", action="store_true",
+                    help="single GPU: run the covariance pass of a scan behind the next scan's sequential side "
+                         "(ekf_set_overlap; measured SLOWER at N=10k, DESIGN.md section 10 - kept for reproduction)")
     ap.add_argument("--batch-filters", type=int, default=65536, help="filters per GPU (BASELINE configs[2])")
     ap.add_argument("--batch-landmarks", type=int, default=20)
     ap.add_argument("--batch-m", type=int, default=20)
@@ -325,6 +328,9 @@ def run_ours(args):
         f = ekf.EkfSlam(n_landmarks=N, device=local, max_scan=m)
         f.set_stream(stream.cuda_stream)
         f.fill_procedural(args.seed, N, side)
+    # --overlap: the covariance pass of scan s runs (out of place, second stream) behind the sequential side of
+    # scan s+1 - ekf_set_overlap; needs a second covariance buffer, stays off when that does not fit
+    overlap = (not sharded) and args.overlap and f.set_overlap(True)
     state0 = f.state()
     n_scans = 2 * (W + K)
     poses, xy, ids = make_workload(state0, N, m, n_scans, args.seed + 100)
@@ -361,6 +367,8 @@ def run_ours(args):
     e0.record(stream)
     for s in range(W, W + K):
         scan_dev(s)
+    if overlap:
+        f.set_overlap(False)      # drain: `stream` waits for the last pass, so e1 closes over ALL the work
     e1.record(stream)
     barrier()
     t1 = time.perf_counter()
@@ -370,6 +378,8 @@ def run_ours(args):
     seq_ms, dd_ms = f.read_timing(K)
     f.enable_timing(0)
     status = f.last_status()
+    if overlap:
+        f.set_overlap(True)
 
     # ---- end to end through the host-buffer call (`e2e`) ---------------------------------------
     e_assoc = []
@@ -434,6 +444,9 @@ def run_ours(args):
                                    f"of the {m}x{n_pad}x2 column panel per scan") if sharded else "1 GPU",
                    "l2": f"inputs larger than L2: Sigma triangle = {float(stored_all.item()) * 8 / 1e9:.2f} GB streamed "
                          "per scan",
+                   "overlap": ("covariance pass of scan s runs out of place on a second stream behind the sequential "
+                               "side of scan s+1 (ekf_set_overlap); the timed region ends after the last pass")
+                              if overlap else "off (pass and sequential phase back to back on one stream)",
                    "association_bit_exact_vs_expected_ids": bool(ok.item())},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 + 16 * m, "d2h_bytes_per_step": 32 + 4 * m,

@@ -72,7 +72,17 @@ int pipe_resources(ekf_filter *f) {
   CK(f, cudaEventCreateWithFlags(&f->done_event, cudaEventDisableTiming));
   CK(f, cudaMallocHost(&f->done_host, sizeof(int)));
   // a sequential CTA and the pass's CTA must fit on one SM together: both ask for the large shared-memory carve-out
+  // ... and so must every other kernel of the sequential side: an SM only changes its L1 / shared-memory split when it
+  // is idle, so a kernel that prefers another split than the resident pass waits for the pass to leave
   CK(f, cudaFuncSetAttribute(ekf_seq_kernel<kSeqThreadsSmall>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared));
+  CK(f, cudaFuncSetAttribute(shard_predict_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared));
+  CK(f, cudaFuncSetAttribute(shard_guess_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared));
+  CK(f, cudaFuncSetAttribute(pipe_extract_cols_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared));
+  CK(f, cudaFuncSetAttribute(ekf_downdate_kernel<64, 2>, cudaFuncAttributePreferredSharedMemoryCarveout,
                              cudaSharedmemCarveoutMaxShared));
   int blocks = (f->N + kSeqThreadsSmall - 1) / kSeqThreadsSmall;
   f->pipe_grid = blocks < f->num_sms ? blocks : f->num_sms;   // one 64-thread CTA per SM beside the pass

@@ -122,9 +122,19 @@ int overlap_round(ekf_filter *f, const double *pose_dev, int mc, const double *x
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
   f->bar_base += (unsigned long long)mc * (unsigned long long)f->pipe_grid;
-  void *args[] = {(void *)&sp};
-  CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel<kSeqThreadsSmall>, dim3(f->pipe_grid),
-                                    dim3(kSeqThreadsSmall), args, seq_smem_bytes(kSeqThreadsSmall), f->stream));
+  // NOT a cooperative launch: the driver holds a cooperative grid back until the device is otherwise idle, which
+  // would put it behind the very pass it is meant to overlap.  Co-residency - all the hand-written grid barrier
+  // needs - holds by construction: at most one CTA per SM, and a CTA fits beside the pass's CTA (registers, shared
+  // memory); the only other kernels that can be resident (the pass on the back stream, other handles' kernels) never
+  // wait for this one.
+  if (env_int("EKF_PIPE_COOP", 0)) {
+    void *args[] = {(void *)&sp};
+    CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel<kSeqThreadsSmall>, dim3(f->pipe_grid),
+                                      dim3(kSeqThreadsSmall), args, seq_smem_bytes(kSeqThreadsSmall), f->stream));
+  } else {
+    ekf_seq_kernel<kSeqThreadsSmall><<<f->pipe_grid, kSeqThreadsSmall, seq_smem_bytes(kSeqThreadsSmall), f->stream>>>(sp);
+    CK(f, cudaGetLastError());
+  }
   f->launches++;
   if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
   CK(f, cudaEventRecord(f->ev_seq[cur], f->stream));
