@@ -72,6 +72,7 @@ def load() -> C.CDLL:
         "ekf_bag_joint_state": (C.c_int, [vp, i32, i64p, ip, i32, dp]),
         "ekf_bag_detections": (C.c_int, [vp, i32, ip, i32, dp, ip, ip]),
         "ekf_selftest_division": (C.c_int, [i32, C.c_uint64, i32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+        "ekf_selftest_atan2": (C.c_int, [i32, C.c_uint64, i32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
         "ekf_create": (C.c_int, [C.POINTER(EkfConfig), C.POINTER(vp)]),
         "ekf_destroy": (C.c_int, [vp]),
         "ekf_set_stream": (C.c_int, [vp, vp]),
@@ -153,6 +154,15 @@ def selftest_division(count: int = 1 << 22, seed: int = 1, device: int = -1):
     st = load().ekf_selftest_division(device, seed, count, C.byref(mis), C.byref(slow))
     if st != 0:
         raise RuntimeError(f"ekf_selftest_division: {status_string(st)}")
+    return int(mis.value), int(slow.value)
+
+
+def selftest_atan2(count: int = 1 << 22, seed: int = 1, device: int = -1):
+    """(mismatches, outside_guard) of the kernels' branch-free atan2 against the CUDA library's on the device."""
+    mis, slow = C.c_uint64(0), C.c_uint64(0)
+    st = load().ekf_selftest_atan2(device, seed, count, C.byref(mis), C.byref(slow))
+    if st != 0:
+        raise RuntimeError(f"ekf_selftest_atan2: {status_string(st)}")
     return int(mis.value), int(slow.value)
 
 

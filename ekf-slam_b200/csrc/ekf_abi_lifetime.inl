@@ -33,7 +33,8 @@ const char *ekf_status_string(int status) {
 
 const char *ekf_version(void) { return "ekf_slam_b200 0.1 (sm_100a)"; }
 
-int ekf_selftest_division(int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard) {
+namespace {
+int selftest_run(int which, int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard) {
   if (!mismatches || !outside_guard || count < 1) return EKF_ERR_INVALID;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return EKF_ERR_NO_DEVICE;
@@ -45,14 +46,23 @@ int ekf_selftest_division(int32_t device, uint64_t seed, int32_t count, uint64_t
   if (cudaMalloc(&d, sizeof(h)) != cudaSuccess) return EKF_ERR_NOMEM;
   cudaError_t e = cudaMemset(d, 0, sizeof(h));
   if (e == cudaSuccess) {
-    ekf::selftest_division_kernel<<<(count + 255) / 256, 256>>>(seed, count, d, d + 1);
+    if (which == 0) ekf::selftest_division_kernel<<<(count + 255) / 256, 256>>>(seed, count, d, d + 1);
+    else ekf::selftest_atan2_kernel<<<(count + 255) / 256, 256>>>(seed, count, d, d + 1);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess) e = cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
   cudaFree(d);
-  if (e != cudaSuccess) { fprintf(stderr, "ekf_selftest_division: %s\n", cudaGetErrorString(e)); return EKF_ERR_CUDA; }
+  if (e != cudaSuccess) { fprintf(stderr, "ekf_selftest: %s\n", cudaGetErrorString(e)); return EKF_ERR_CUDA; }
   *mismatches = h[0]; *outside_guard = h[1];
   return EKF_OK;
+}
+}  // namespace
+
+int ekf_selftest_division(int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard) {
+  return selftest_run(0, device, seed, count, mismatches, outside_guard);
+}
+int ekf_selftest_atan2(int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard) {
+  return selftest_run(1, device, seed, count, mismatches, outside_guard);
 }
 
 int ekf_destroy(ekf_filter *f) {

@@ -76,6 +76,10 @@ const char *ekf_version(void);
  * *mismatches = pairs inside the fast path's guard whose quotient differs in any bit from IEEE `a / b` (must be 0);
  * *outside_guard = pairs the guard sends to the plain division. */
 int ekf_selftest_division(int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard);
+/* The same for the branch-free atan2 behind the expected bearing (slam.cpp:224-227 / :367-370): against the CUDA math
+ * library's atan2 on hashed (y, x) pairs - all exponents, specials, and the filter's own range.  *mismatches must be 0;
+ * *outside_guard = pairs (non-finite, both zero, extreme ratios) that go to the library call. */
+int ekf_selftest_atan2(int32_t device, uint64_t seed, int32_t count, uint64_t *mismatches, uint64_t *outside_guard);
 
 /* ---- lifetime: replaces slam.cpp:127-139 ------------------------------------------------ */
 int ekf_create(const ekf_config *cfg, ekf_filter **out);

@@ -319,3 +319,12 @@ def test_shared_reciprocal_division_is_ieee_division():
         mismatches, outside = ekf_slam_b200.selftest_division(count=1 << 22, seed=seed)
         assert mismatches == 0
         assert outside < (1 << 22)          # the fast path is actually taken
+
+
+def test_branch_free_atan2_is_the_library_atan2():
+    """The expected bearing (slam.cpp:224-227 / :367-370) is formed with a branch-free restatement of the CUDA math
+    library's atan2: bit for bit the library's result wherever its guard admits the arguments."""
+    for seed in (1, 2, 3):
+        mismatches, outside = ekf_slam_b200.selftest_atan2(count=1 << 22, seed=seed)
+        assert mismatches == 0
+        assert outside < (1 << 20)          # the fast path is what runs on the filter's own range
