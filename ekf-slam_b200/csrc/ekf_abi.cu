@@ -63,6 +63,8 @@ struct ekf_filter {
   // staging for the host-pointer entry points
   unsigned char *io_dev = nullptr, *io_host = nullptr;   // inputs: pose | xy | ids | action
   unsigned char *res_dev = nullptr, *res_host = nullptr; // results: pose | cnt | status | assoc
+  unsigned char *res_host_dev = nullptr;   // device-side address of res_host (mapped pinned memory)
+  bool res_direct = false;                 // this scan's kernels write their results straight into res_host
   // host-buffer scans hand their results back as soon as the sequential phase is done: the copy is
   // enqueued between the last sequential launch and its covariance pass, the caller waits on this event
   cudaEvent_t res_event = nullptr;
@@ -158,10 +160,13 @@ int ensure_io(ekf_filter *f, int m) {
   if (res.total > f->res_cap) {
     if (f->res_dev) cudaFree(f->res_dev);
     if (f->res_host) cudaFreeHost(f->res_host);
-    f->res_dev = nullptr; f->res_host = nullptr; f->res_cap = 0;
+    f->res_dev = nullptr; f->res_host = nullptr; f->res_host_dev = nullptr; f->res_cap = 0;
     const size_t cap = align_up(res.total * 2, 256);
     CK(f, cudaMalloc(&f->res_dev, cap));
     CK(f, cudaMallocHost(&f->res_host, cap));
+    void *mapped = nullptr;
+    f->res_host_dev = cudaHostGetDevicePointer(&mapped, f->res_host, 0) == cudaSuccess ? (unsigned char *)mapped : nullptr;
+    if (!f->res_host_dev) cudaGetLastError();
     f->res_cap = cap;
   }
   return EKF_OK;

@@ -7,9 +7,11 @@ namespace {
 int results_out(ekf_filter *f) {
   const size_t total = f->res_pending;
   f->res_pending = 0;
-  CK(f, cudaMemcpyAsync(f->res_dev + ResLayout(0).status, f->status, sizeof(int), cudaMemcpyDeviceToDevice, f->stream));
-  CK(f, cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
-  CK(f, cudaMemcpyAsync(f->res_host, f->res_dev, total, cudaMemcpyDeviceToHost, f->stream));
+  if (!f->res_direct) {
+    CK(f, cudaMemcpyAsync(f->res_dev + ResLayout(0).status, f->status, sizeof(int), cudaMemcpyDeviceToDevice, f->stream));
+    CK(f, cudaMemsetAsync(f->status, 0, sizeof(int), f->stream));
+    CK(f, cudaMemcpyAsync(f->res_host, f->res_dev, total, cudaMemcpyDeviceToHost, f->stream));
+  }   // else: the finishing sequential launch stored pose / count / association / status in res_host itself
   CK(f, cudaEventRecord(f->res_event, f->stream));
   return EKF_OK;
 }
@@ -28,6 +30,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   sp.pose = pose_dev; sp.xy = xy_dev; sp.ids = ids_dev; sp.action = action_dev;
   sp.m = mc; sp.do_predict = do_predict; sp.finish = finish;
   sp.assoc_out = assoc_dev; sp.pose_out = pose_out_dev; sp.cnt_out = cnt_out_dev;
+  sp.status_out = f->res_direct ? reinterpret_cast<int *>(f->res_host_dev + ResLayout(0).status) : nullptr;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
   f->bar_base += (unsigned long long)(mc > 0 ? mc : 1) * (unsigned long long)f->seq_grid;
@@ -263,13 +266,18 @@ int scan_host(ekf_filter *f, const double *pose, int m, const double *xy, const 
   }
   CK(f, cudaMemcpyAsync(f->io_dev, f->io_host, in.total, cudaMemcpyHostToDevice, f->stream));
   f->res_pending = res.total;
+  // classic path with sightings: the sequential kernel stores its few result words straight into the mapped pinned
+  // buffer (posted PCIe writes) - no copy operations between it and the covariance pass (they cost ~3 us each of
+  // GPU time line); the caller still waits for the event recorded right after that launch
+  f->res_direct = m > 0 && !f->overlap && f->res_host_dev != nullptr;
+  unsigned char *rb = f->res_direct ? f->res_host_dev : f->res_dev;
   rc = scan_device(f, pose ? reinterpret_cast<const double *>(f->io_dev + in.pose) : nullptr, m,
                    reinterpret_cast<const double *>(f->io_dev + in.xy),
                    ids ? reinterpret_cast<const int32_t *>(f->io_dev + in.ids) : nullptr,
                    action ? reinterpret_cast<const uint8_t *>(f->io_dev + in.action) : nullptr,
-                   reinterpret_cast<int32_t *>(f->res_dev + res.assoc), reinterpret_cast<double *>(f->res_dev + res.pose),
-                   reinterpret_cast<int *>(f->res_dev + res.cnt));
-  if (rc != EKF_OK) { f->res_pending = 0; return rc; }
+                   reinterpret_cast<int32_t *>(rb + res.assoc), reinterpret_cast<double *>(rb + res.pose),
+                   reinterpret_cast<int *>(rb + res.cnt));
+  if (rc != EKF_OK) { f->res_pending = 0; f->res_direct = false; return rc; }
   if (f->res_pending) {                           // a scan without measurements has no finishing launch
     rc = results_out(f);
     if (rc != EKF_OK) return rc;
@@ -277,6 +285,7 @@ int scan_host(ekf_filter *f, const double *pose, int m, const double *xy, const 
   // the covariance pass of this scan may still be running: it is stream-ordered before anything that
   // reads Sigma, and the next call's kernels queue up behind it
   CK(f, cudaEventSynchronize(f->res_event));
+  f->res_direct = false;
   if (out_assoc && m > 0) memcpy(out_assoc, f->res_host + res.assoc, (size_t)4 * m);
   if (out_count) memcpy(out_count, f->res_host + res.cnt, 4);
   if (out_pose) memcpy(out_pose, f->res_host + res.pose, 24);

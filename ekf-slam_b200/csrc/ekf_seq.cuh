@@ -83,6 +83,7 @@ struct SeqParams {
   int *assoc_out;         // device m or nullptr
   double *pose_out;       // device 3 (always written)
   int *cnt_out;           // device 1 (always written)
+  int *status_out;        // nullptr, or where the finishing launch hands over (and clears) the latched status
   // storage geometry of this handle's rows (whole matrix, or one row shard)
   EkfLay lay;
   // row-sharded handles (ekf_shard.cuh): side_mode = 1 means Pp / D are persistent and current (Sigma
@@ -724,6 +725,7 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
     p.pose_out[0] = s_ps[0]; p.pose_out[1] = s_ps[1]; p.pose_out[2] = s_ps[2];
     if (p.finish && done == p.m) { p.prev_xy[0] = s_ps[1]; p.prev_xy[1] = s_ps[2]; }
     if (p.done_out) *p.done_out = done;
+    if (p.status_out && p.finish) *p.status_out = atomicExch(p.status, 0);
   }
 }
 
