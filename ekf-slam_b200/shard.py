@@ -138,8 +138,8 @@ class _Driver:
                 self._h_ids.numpy()[:m] = np.asarray(ids, dtype=np.int32)
                 self._d_ids[:m].copy_(self._h_ids[:m], non_blocking=True)
                 ids_t = self._d_ids[:m]
-            self._r_assoc.fill_(-7)
             hres = self._h_res.numpy()
+            hbase = self._h_res.data_ptr()     # pinned + mapped: the last handle's kernel stores its results here
             t0, first, rounds = 0, True, 0
             while t0 < m:
                 rem = m - t0
@@ -150,10 +150,14 @@ class _Driver:
                 hs = self.handles()
                 for q, h in enumerate(hs):
                     tail = q == len(hs) - 1       # the last handle's finish hands the results to the host
-                    h.shard_scan_finish(self._r_assoc[t0:].data_ptr(), self._r_done.data_ptr(),
-                                        self._r_pose.data_ptr(), self._r_cnt.data_ptr(),
-                                        self._d_res.data_ptr() if tail else 0, self._h_res.data_ptr() if tail else 0,
-                                        self._d_res.numel() if tail else 0, self._res_ev.cuda_event if tail else 0)
+                    if tail:
+                        # association / done / pose / count go straight into the mapped pinned buffer (a few posted
+                        # PCIe stores from the sequential kernel): no copy operation between it and the covariance pass
+                        h.shard_scan_finish(hbase + 32 + 4 * t0, hbase + 28, hbase, hbase + 24, 0, 0, 0,
+                                            self._res_ev.cuda_event)
+                    else:
+                        h.shard_scan_finish(self._r_assoc[t0:].data_ptr(), self._r_done.data_ptr(),
+                                            self._r_pose.data_ptr(), self._r_cnt.data_ptr(), 0, 0, 0, 0)
                 # results are final after the sequential phase; the covariance pass keeps running while the
                 # host reads them and prepares the next round / scan
                 self._res_ev.synchronize()
