@@ -60,6 +60,11 @@ struct ekf_filter {
   unsigned long long bar_base = 0;
   double *slot_d = nullptr, *slot_rec = nullptr;
   int *slot_k = nullptr;
+  // hot-winner area of the sequential kernel (SeqParams::hot_hdr); classic path, 64-thread shape only
+  unsigned long long *hot_hdr = nullptr;
+  double *hot_rec = nullptr;
+  double2 *hot_w = nullptr;
+  bool seq_hot = false;
   // staging for the host-pointer entry points
   unsigned char *io_dev = nullptr, *io_host = nullptr;   // inputs: pose | xy | ids | action
   unsigned char *res_dev = nullptr, *res_host = nullptr; // results: pose | cnt | status | assoc

@@ -79,6 +79,7 @@ int ekf_destroy(ekf_filter *f) {
       if (f->peer_ipc[q]) cudaIpcCloseMemHandle(f->peer_ipc[q]);
     cudaFree(f->xchg); cudaFree(f->push_done);
     cudaFree(f->prev_xy); cudaFree(f->bar); cudaFree(f->slot_d); cudaFree(f->slot_k); cudaFree(f->slot_rec);
+    cudaFree(f->hot_hdr); cudaFree(f->hot_rec); cudaFree(f->hot_w);
     cudaFree(f->io_dev); cudaFree(f->res_dev); cudaFree(f->scratch_dev);
     if (f->io_host) cudaFreeHost(f->io_host);
     if (f->res_host) cudaFreeHost(f->res_host);
@@ -151,14 +152,15 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
 
   // grids: sequential kernel = cooperative (shape chosen from N, see ekf_seq.cuh); covariance pass = one CTA per SM
   CKC(cudaFuncSetAttribute(ekf_seq_kernel<kSeqThreadsSmall>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)seq_smem_bytes(kSeqThreadsSmall)));
+                           (int)seq_smem_bytes(kSeqThreadsSmall, true)));
   CKC(cudaFuncSetAttribute(ekf_seq_kernel<kSeqThreadsLarge>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)seq_smem_bytes(kSeqThreadsLarge)));
   // co-resident CTAs the cooperative launch may use (occupancy of the kernel with its dynamic smem), capped by
   // what one warp can scan in the arg-min slot read
   int seq_occ = 1;
+  f->seq_hot = env_int("EKF_SEQ_HOT", 1) != 0;
   CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&seq_occ, ekf_seq_kernel<kSeqThreadsSmall>, kSeqThreadsSmall,
-                                                    seq_smem_bytes(kSeqThreadsSmall)));
+                                                    seq_smem_bytes(kSeqThreadsSmall, f->seq_hot)));
   if (seq_occ < 1) seq_occ = 1;
   if (seq_occ > kSeqCtasPerSm) seq_occ = kSeqCtasPerSm;
   int seq_cap = f->num_sms * seq_occ;
@@ -183,6 +185,12 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   CKC(cudaMalloc(&f->slot_d, (size_t)kSlotReps * 2 * seq_cap * sizeof(double)));
   CKC(cudaMalloc(&f->slot_k, (size_t)kSlotReps * 2 * seq_cap * sizeof(int)));
   CKC(cudaMalloc(&f->slot_rec, (size_t)kSlotReps * 2 * seq_cap * kRecStride * sizeof(double)));
+  CKC(cudaMalloc(&f->hot_hdr, (size_t)kSlotReps * 2 * sizeof(unsigned long long)));
+  CKC(cudaMemset(f->hot_hdr, 0, (size_t)kSlotReps * 2 * sizeof(unsigned long long)));
+  CKC(cudaMalloc(&f->hot_rec, (size_t)kSlotReps * 2 * kRecStride * sizeof(double)));
+  CKC(cudaMemset(f->hot_rec, 0, (size_t)kSlotReps * 2 * kRecStride * sizeof(double)));
+  CKC(cudaMalloc(&f->hot_w, (size_t)kSlotReps * 2 * kMaxK2 * sizeof(double2)));
+  CKC(cudaMemset(f->hot_w, 0, (size_t)kSlotReps * 2 * kMaxK2 * sizeof(double2)));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)dd_smem_bytes(64, kMaxK2)));
   CKC(cudaFuncSetAttribute(ekf_downdate_kernel<64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -34,6 +34,8 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
   f->bar_base += (unsigned long long)(mc > 0 ? mc : 1) * (unsigned long long)f->seq_grid;
+  const bool hot = f->seq_hot && f->seq_threads == kSeqThreadsSmall;
+  if (hot) { sp.hot_hdr = f->hot_hdr; sp.hot_rec = f->hot_rec; sp.hot_w = f->hot_w; }
 
   const bool timed = f->ev_cap > 0 && mc > 0;
   const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 4 : 0;
@@ -42,7 +44,7 @@ int launch_chunk(ekf_filter *f, const double *pose_dev, int do_predict, int mc, 
   const void *seq_fn = f->seq_threads == kSeqThreadsSmall ? (const void *)ekf_seq_kernel<kSeqThreadsSmall>
                                                           : (const void *)ekf_seq_kernel<kSeqThreadsLarge>;
   CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
-                                    seq_smem_bytes(f->seq_threads), f->stream));
+                                    seq_smem_bytes(f->seq_threads, hot), f->stream));
   f->launches++;
   if (timed) { CK(f, cudaEventRecord(f->ev[slot + 1], f->stream)); CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); }
   if (finish && f->res_pending) {                        // everything the caller reads back is final here

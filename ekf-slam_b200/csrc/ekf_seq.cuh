@@ -53,7 +53,10 @@ constexpr int kSeqCtasPerSm = 2;          // cooperative grid: at most this many
 constexpr int kMaxChunkM = 24;            // measurements per sequential launch / covariance pass
 constexpr int kMaxK2 = 2 * kMaxChunkM;    // panel columns in use per pass
 // dynamic shared memory of ekf_seq_kernel: the own-landmark V rows, [kMaxChunkM][2][NT] double2
-constexpr size_t seq_smem_bytes(int nt) { return (size_t)kMaxChunkM * 2 * nt * sizeof(double2); }
+// (+ the same for the W rows when the launch uses the hot-winner area, see SeqParams::hot_hdr)
+constexpr size_t seq_smem_bytes(int nt, bool hot = false) {
+  return (size_t)kMaxChunkM * 2 * nt * sizeof(double2) * (hot ? 2 : 1);
+}
 
 // status codes latched on the device (values of ekf_status in include/ekf_slam_b200.h)
 constexpr int kErrCapacity = 2;
@@ -102,6 +105,15 @@ struct SeqParams {
   double *slot_d;  // [kSlotReps][2][gridDim]
   int *slot_k;     // [kSlotReps][2][gridDim]
   double *slot_rec;  // [kSlotReps][2][gridDim][kRecStride]: the slot candidate's update record
+  // Hot-winner area (nullptr = off).  After the barrier the decision needs the slots (one L2 round trip) and THEN the
+  // winner's record and panel-row history (a second, dependent one).  A CTA whose best candidate is under the
+  // threshold - normally exactly one CTA per matched sighting - therefore also pushes that record and its W-row
+  // history here before the barrier, and the readers load this area TOGETHER with the slots.  The header counts the
+  // claimants of this measurement (tag = the barrier target, unique and increasing): the preloaded copy is used
+  // only when there is exactly one and it is the arg-min winner; anything else takes the two-round-trip path.
+  unsigned long long *hot_hdr;   // [kSlotReps][2]: tag * 256 + claimants
+  double *hot_rec;               // [kSlotReps][2][kRecStride]: record, [kRecDoubles] = landmark index
+  double2 *hot_w;                // [kSlotReps][2][kMaxK2]: (W[a][q], W[a+1][q]) of the claimant's landmark
 };
 constexpr int kSlotReps = 8;
 constexpr int kMaxSlotsPerLane = 5;       // gridDim <= 32 * kMaxSlotsPerLane (one CTA per SM, 148 SMs)
@@ -179,6 +191,9 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
   // V rows (a, a+1) of the thread's FIRST landmark, [measurement][row][thread] as (column 2t, 2t+1)
   // pairs: the deferred-downdate correction of phase D reads them back every measurement
   extern __shared__ double2 s_vown[];
+  // the same for its W rows (hot-winner launches only: the claimant pushes this history, see SeqParams::hot_hdr)
+  const bool hot = p.hot_hdr != nullptr;
+  double2 *const s_wown = s_vown + kMaxChunkM * 2 * kSeqThreads;
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -350,6 +365,28 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
           p.slot_d[(lane * 2 + par) * G + blockIdx.x] = c.d;
           p.slot_k[(lane * 2 + par) * G + blockIdx.x] = c.k;
         }
+        // hot-winner claim: the candidate is a match on its own evidence and it is its thread's first landmark
+        // (the one whose panel rows live in shared memory)
+        if (hot && c.d <= p.thr && c.k < cnt && c.k / kSeqThreads == (int)blockIdx.x) {
+          const int otid = c.k - (int)blockIdx.x * kSeqThreads;
+          if (lane <= kRecDoubles) {
+            const double v = lane < kRecDoubles ? s_wrec[bw][lane] : (double)c.k;
+#pragma unroll
+            for (int r = 0; r < kSlotReps; ++r) p.hot_rec[(r * 2 + par) * kRecStride + lane] = v;
+          }
+          for (int q = lane; q < 2 * t; q += 32) {
+            // panel column q = 2 s2 + h of rows a, a+1: component h of the (column 2 s2, 2 s2 + 1) pairs
+            const double2 ra = s_wown[(q & ~1) * kSeqThreads + otid], rb = s_wown[((q & ~1) + 1) * kSeqThreads + otid];
+            const double2 v = (q & 1) ? make_double2(ra.y, rb.y) : make_double2(ra.x, rb.x);
+#pragma unroll
+            for (int r = 0; r < kSlotReps; ++r) p.hot_w[(r * 2 + par) * kMaxK2 + q] = v;
+          }
+          if (lane < kSlotReps) {
+            const unsigned long long tag = p.bar_base + (unsigned long long)(t + 1) * gridDim.x;
+            atomicMax(p.hot_hdr + lane * 2 + par, tag << 8);
+            atomicAdd(p.hot_hdr + lane * 2 + par, 1ULL);
+          }
+        }
       }
     }
 
@@ -374,6 +411,19 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
           const int b = lane + 32 * i;
           od[i] = INFINITY; ok[i] = 0x7fffffff;
           if (b < G) { od[i] = ldcg_d(sd + b); ok[i] = __ldcg(sk + b); }
+        }
+        // hot-winner area, in the same round trip: header + record (warp 0) / panel-row history (warp 1)
+        unsigned long long hhdr = 0;
+        double hval = 0.0;
+        double2 hw0 = make_double2(0.0, 0.0), hw1 = hw0;
+        if (hot) {
+          const int hs = rep * 2 + par;
+          asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(hhdr) : "l"(p.hot_hdr + hs));
+          if (lane <= kRecDoubles) hval = ldcg_d(p.hot_rec + hs * kRecStride + (warp == 0 ? lane : kRecDoubles));
+          if (warp == 1) {
+            if (lane < 2 * t) hw0 = __ldcg(p.hot_w + hs * kMaxK2 + lane);
+            if (lane + 32 < 2 * t) hw1 = __ldcg(p.hot_w + hs * kMaxK2 + lane + 32);
+          }
         }
         Cand c{INFINITY, 0x7fffffff};
         int bstar = 0;
@@ -406,15 +456,26 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
         // strictly smaller value: slam.cpp:406-408,418-440
         fast = (c.d <= p.thr && c.k < cnt);
         if (tid == 0) s_fast = fast ? 1 : 0;
+        // the preloaded copy is the winner's iff this measurement had exactly one claimant and it is the winner
+        bool hot_ok = false;
+        if (hot && fast) {
+          const unsigned long long tag = p.bar_base + (unsigned long long)(t + 1) * gridDim.x;
+          const double hk = __shfl_sync(0xffffffffu, hval, warp == 0 ? kRecDoubles : 0);
+          hot_ok = (hhdr == ((tag << 8) | 1ULL)) && (hk == (double)c.k);
+        }
         if (fast) {
           jfast = c.k;
           if (warp == 0) {
             if (lane < kRecDoubles)
-              s_b.rec[lane] = ldcg_d(p.slot_rec + (int64_t)((rep * 2 + par) * G + bstar) * kRecStride + lane);
+              s_b.rec[lane] = hot_ok ? hval
+                                     : ldcg_d(p.slot_rec + (int64_t)((rep * 2 + par) * G + bstar) * kRecStride + lane);
             if (lane == 0) {
               s_b.j = jfast; s_b.is_new = 0;
               if (blockIdx.x == 0 && p.assoc_out) p.assoc_out[t] = jfast;
             }
+          } else if (hot_ok) {
+            if (lane < 2 * t) { s_wa[lane] = hw0.x; s_wb[lane] = hw0.y; }
+            if (lane + 32 < 2 * t) { s_wa[lane + 32] = hw1.x; s_wb[lane + 32] = hw1.y; }
           } else {
             // panel history of the chosen landmark's two rows (column operand of the correction):
             // 8 doubles per k-step, columns q < 2t; at most 3 per lane, all in flight together
@@ -567,6 +628,10 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
       }
       s_vown[(2 * t) * kSeqThreads + tid] = make_double2(0.0, 0.0);
       s_vown[(2 * t + 1) * kSeqThreads + tid] = make_double2(0.0, 0.0);
+      if (hot) {
+        s_wown[(2 * t) * kSeqThreads + tid] = make_double2(0.0, 0.0);
+        s_wown[(2 * t + 1) * kSeqThreads + tid] = make_double2(0.0, 0.0);
+      }
     } else {
       Lin L;
       L.h0[0] = 0.0; L.h1[0] = -1.0;
@@ -679,6 +744,10 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
           o_pa = pa; o_pb = pbr; o_dk = dk; o_lm = lm;
           s_vown[(2 * t) * kSeqThreads + tid] = make_double2(ka0, ka1);
           s_vown[(2 * t + 1) * kSeqThreads + tid] = make_double2(kb0, kb1);
+          if (hot) {
+            s_wown[(2 * t) * kSeqThreads + tid] = make_double2(ga0, ga1);
+            s_wown[(2 * t + 1) * kSeqThreads + tid] = make_double2(gb0, gb1);
+          }
         }
       }
     }

@@ -328,3 +328,45 @@ def test_branch_free_atan2_is_the_library_atan2():
         mismatches, outside = ekf_slam_b200.selftest_atan2(count=1 << 22, seed=seed)
         assert mismatches == 0
         assert outside < (1 << 20)          # the fast path is what runs on the filter's own range
+
+
+def _hot_run(hot, monkeypatch, twin):
+    """4 scans of a 300-landmark procedural map; with `twin`, landmark 200 is moved next to landmark 5 so that two CTAs
+    of the sequential kernel hold a candidate under the threshold for the same sighting."""
+    monkeypatch.setenv("EKF_SEQ_HOT", "1" if hot else "0")
+    g, o, grid_w = _procedural_pair(300, 290)
+    if twin:
+        st = g.state()
+        st[3 + 2 * 200: 5 + 2 * 200] = st[3 + 2 * 5: 5 + 2 * 5] + np.array([2e-4, -1e-4])
+        g.set_state(st); o.state[:] = st
+    rng = np.random.default_rng(5)
+    pose = np.array([0.3, grid_w / 2.0, grid_w / 2.0])
+    if twin:
+        pose[1:] = o.state[3 + 2 * 5: 5 + 2 * 5] + np.array([0.4, 0.3])
+    g.set_previous_xy(pose[1], pose[2]); o.set_prev(pose[1], pose[2])
+    assoc = []
+    for s in range(4):
+        pose = pose + np.array([0.05, 0.1, 0.07])
+        near, xy = _scan_inputs(o.state, 290, grid_w, rng, 20, pose)
+        aG, cG, _ = g.scan(pose, xy)
+        o.predict(*pose)
+        aO = o.update_unknown(xy)
+        assert list(aG) == list(aO) and cG == o.count
+        assoc.append(list(aG))
+    out = assoc, g.state(), g.sigma()
+    assert rel_fro(out[1], o.state) <= TOL and rel_fro(out[2], o.sigma) <= TOL
+    g.close(); o.close()
+    return out
+
+
+@pytest.mark.parametrize("twin", [False, True])
+def test_hot_winner_area_changes_nothing(monkeypatch, twin):
+    """The sequential kernel's hot-winner area (record + panel rows pushed by the one CTA under the threshold, read in
+    the same round trip as the slots) carries the same numbers as the two-round-trip path: bit-identical filters,
+    also when two CTAs claim the same sighting (twin landmarks 195 apart in index) and the area must be ignored."""
+    a = _hot_run(True, monkeypatch, twin)
+    b = _hot_run(False, monkeypatch, twin)
+    assert a[0] == b[0]
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    if twin:
+        assert any(5 in s for s in a[0])        # the twin was sighted; the lower index wins
