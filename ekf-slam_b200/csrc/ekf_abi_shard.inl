@@ -180,6 +180,8 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   sp.done_out = done_dev ? done_dev : f->done_dev;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
+  const bool hot = f->seq_hot && f->seq_threads == kSeqThreadsSmall;
+  if (hot) { sp.hot_hdr = f->hot_hdr; sp.hot_rec = f->hot_rec; sp.hot_w = f->hot_w; }
   f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
   f->pend_m = -1;
 
@@ -190,7 +192,7 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   const void *seq_fn = f->seq_threads == kSeqThreadsSmall ? (const void *)ekf_seq_kernel<kSeqThreadsSmall>
                                                           : (const void *)ekf_seq_kernel<kSeqThreadsLarge>;
   CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
-                                    seq_smem_bytes(f->seq_threads), f->stream));
+                                    seq_smem_bytes(f->seq_threads, hot), f->stream));
   f->launches++;
   if (timed) { CK(f, cudaEventRecord(f->ev[slot + 1], f->stream)); CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); }
   // association / done / pose / count are final here: hand them to the host before the covariance pass
