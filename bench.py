@@ -273,12 +273,29 @@ def bench_batched(args, torch, ekf, stream, local, world, dist):
         exp = np.take_along_axis(pos, ids[s], axis=1)
         ok = ok and bool((d_assoc[s, :, :ids[s].shape[1]].cpu().numpy() == exp).all())
     ok = ok and g.last_status() == 0 and int(d_cnt.min()) == N
+    # end to end: inputs in pinned host memory (as a producer would leave them), results into pinned host arrays
+    def pin(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        return t, t.numpy()
+    keep = []
+    p_in = {}
+    for s in range(W + K, W + 2 * K):
+        tp, ap = pin(h_pose[s]); tx, ax = pin(h_xy[s])
+        keep += [tp, tx]; p_in[s] = (ap, ax)
+    t_a = torch.empty((B, m), dtype=torch.int32).pin_memory()
+    t_c = torch.empty((B,), dtype=torch.int32).pin_memory()
+    t_p = torch.empty((B, 3), dtype=torch.float64).pin_memory()
+    out = (t_a.numpy(), t_c.numpy(), t_p.numpy())
+    # (the filters are in steady state - all landmarks mapped - so a sighting set may be replayed as warm-up)
+    for s in range(W + K, W + K + 3):
+        g.step(p_in[s][0], p_in[s][1], out=out)
     barrier()
     t0 = time.perf_counter()
     for s in range(W + K, W + 2 * K):
-        g.step(h_pose[s], h_xy[s])
+        g.step(p_in[s][0], p_in[s][1], out=out)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1000.0
+    ok = ok and int(out[1].min()) == N
     tt = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)

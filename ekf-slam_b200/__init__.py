@@ -466,9 +466,10 @@ class EkfBatch:
     def last_status(self) -> int:
         return self._L.ekf_batch_last_status(self._h)
 
-    def step(self, poses, xy, ids=None, m_count=None, allow=()):
+    def step(self, poses, xy, ids=None, m_count=None, allow=(), out=None):
         """poses [B,3] (theta, x, y); xy [B,m,2]; ids [B,m] or None; m_count [B] or None.
-        Returns (assoc [B,m], count [B], pose_after [B,3])."""
+        Returns (assoc [B,m], count [B], pose_after [B,3]).  Page-locked inputs / `out` arrays (e.g. numpy views of
+        torch pin_memory tensors) are copied from / into directly, pageable ones through the handle's staging."""
         B = self.n_filters
         poses = np.ascontiguousarray(poses, dtype=np.float64).reshape(B, 3)
         xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(B, -1, 2)
@@ -480,9 +481,14 @@ class EkfBatch:
         if m_count is not None:
             m_count = np.ascontiguousarray(m_count, dtype=np.int32).reshape(B)
             mcp = _ip(m_count)
-        assoc = np.full((B, m), -7, dtype=np.int32)
-        cnt = np.zeros(B, dtype=np.int32)
-        pose = np.zeros((B, 3))
+        if out is None:
+            assoc = np.full((B, m), -7, dtype=np.int32)
+            cnt = np.zeros(B, dtype=np.int32)
+            pose = np.zeros((B, 3))
+        else:       # caller-owned (ideally page-locked: copied into directly) int32 [B,m], int32 [B], float64 [B,3]
+            assoc, cnt, pose = out
+            assert assoc.dtype == np.int32 and assoc.shape == (B, m) and assoc.flags.c_contiguous
+            assert cnt.dtype == np.int32 and cnt.shape == (B,) and pose.dtype == np.float64 and pose.shape == (B, 3)
         self._check(self._L.ekf_batch_step(self._h, _dp(poses), m, _dp(xy), idp, mcp, _ip(assoc), _ip(cnt),
                                            _dp(pose)), "ekf_batch_step", allow)
         return assoc, cnt, pose

@@ -253,11 +253,26 @@ int ekf_batch_step(ekf_batch *b, const double *poses, int32_t m, const double *x
   if (rc != EKF_OK) return rc;
   const BatchIo io(b->B, m);
   const size_t B = (size_t)b->B;
-  memcpy(b->io_host + io.pose, poses, 24 * B);
-  memcpy(b->io_host + io.xy, xy, 16 * B * m);
-  if (ids) memcpy(b->io_host + io.ids, ids, 4 * B * m);
-  if (m_count) memcpy(b->io_host + io.mc, m_count, 4 * B);
-  CKB(b, cudaMemcpyAsync(b->io_dev, b->io_host, io.total, cudaMemcpyHostToDevice, b->stream));
+  // Caller buffers that are page-locked (cudaHostAlloc / cudaHostRegister; torch pin_memory) are copied from / to
+  // directly; pageable ones go through the handle's pinned staging (one extra host memcpy each way).
+  auto pinned = [](const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+  };
+  const bool in_direct = pinned(poses) && pinned(xy) && (!ids || pinned(ids)) && (!m_count || pinned(m_count));
+  if (in_direct) {
+    CKB(b, cudaMemcpyAsync(b->io_dev + io.pose, poses, 24 * B, cudaMemcpyHostToDevice, b->stream));
+    CKB(b, cudaMemcpyAsync(b->io_dev + io.xy, xy, 16 * B * m, cudaMemcpyHostToDevice, b->stream));
+    if (ids) CKB(b, cudaMemcpyAsync(b->io_dev + io.ids, ids, 4 * B * m, cudaMemcpyHostToDevice, b->stream));
+    if (m_count) CKB(b, cudaMemcpyAsync(b->io_dev + io.mc, m_count, 4 * B, cudaMemcpyHostToDevice, b->stream));
+  } else {
+    memcpy(b->io_host + io.pose, poses, 24 * B);
+    memcpy(b->io_host + io.xy, xy, 16 * B * m);
+    if (ids) memcpy(b->io_host + io.ids, ids, 4 * B * m);
+    if (m_count) memcpy(b->io_host + io.mc, m_count, 4 * B);
+    CKB(b, cudaMemcpyAsync(b->io_dev, b->io_host, io.total, cudaMemcpyHostToDevice, b->stream));
+  }
   rc = batch_launch(b, reinterpret_cast<const double *>(b->io_dev + io.pose), m,
                     reinterpret_cast<const double *>(b->io_dev + io.xy),
                     ids ? reinterpret_cast<const int32_t *>(b->io_dev + io.ids) : nullptr,
@@ -268,11 +283,22 @@ int ekf_batch_step(ekf_batch *b, const double *poses, int32_t m, const double *x
   if (rc != EKF_OK) return rc;
   CKB(b, cudaMemcpyAsync(b->res_dev + io.r_status, b->status, sizeof(int), cudaMemcpyDeviceToDevice, b->stream));
   CKB(b, cudaMemsetAsync(b->status, 0, sizeof(int), b->stream));
-  CKB(b, cudaMemcpyAsync(b->res_host, b->res_dev, io.r_total, cudaMemcpyDeviceToHost, b->stream));
-  CKB(b, cudaStreamSynchronize(b->stream));
-  if (out_assoc) memcpy(out_assoc, b->res_host + io.r_assoc, 4 * B * m);
-  if (out_count) memcpy(out_count, b->res_host + io.r_cnt, 4 * B);
-  if (out_pose) memcpy(out_pose, b->res_host + io.r_pose, 24 * B);
+  const bool out_direct = (!out_assoc || pinned(out_assoc)) && (!out_count || pinned(out_count)) &&
+                          (!out_pose || pinned(out_pose));
+  if (out_direct) {
+    if (out_assoc) CKB(b, cudaMemcpyAsync(out_assoc, b->res_dev + io.r_assoc, 4 * B * m, cudaMemcpyDeviceToHost, b->stream));
+    if (out_count) CKB(b, cudaMemcpyAsync(out_count, b->res_dev + io.r_cnt, 4 * B, cudaMemcpyDeviceToHost, b->stream));
+    if (out_pose) CKB(b, cudaMemcpyAsync(out_pose, b->res_dev + io.r_pose, 24 * B, cudaMemcpyDeviceToHost, b->stream));
+    CKB(b, cudaMemcpyAsync(b->res_host + io.r_status, b->res_dev + io.r_status, sizeof(int), cudaMemcpyDeviceToHost,
+                           b->stream));
+    CKB(b, cudaStreamSynchronize(b->stream));
+  } else {
+    CKB(b, cudaMemcpyAsync(b->res_host, b->res_dev, io.r_total, cudaMemcpyDeviceToHost, b->stream));
+    CKB(b, cudaStreamSynchronize(b->stream));
+    if (out_assoc) memcpy(out_assoc, b->res_host + io.r_assoc, 4 * B * m);
+    if (out_count) memcpy(out_count, b->res_host + io.r_cnt, 4 * B);
+    if (out_pose) memcpy(out_pose, b->res_host + io.r_pose, 24 * B);
+  }
   int dev_status = 0;
   memcpy(&dev_status, b->res_host + io.r_status, 4);
   return dev_status;

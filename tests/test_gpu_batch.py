@@ -111,3 +111,35 @@ def test_batch_capacity_and_bad_id_are_statuses():
         assert e.value.status == m.EKF_ERR_BAD_ID
         L = m.load()
         assert L.ekf_batch_step(g._h, None, 0, None, None, None, None, None, None) == m.EKF_ERR_INVALID
+
+
+def test_page_locked_caller_buffers_are_used_directly_and_give_the_same_filters():
+    """ekf_batch_step copies from / into page-locked caller arrays without staging; pageable ones go through the
+    handle's pinned buffer.  Both routes must leave identical filters and results."""
+    import torch
+    B, N, m = 96, 12, 9
+    rng = np.random.default_rng(3)
+    fields = synth.batch_fields(B, N, seed=5)
+    runs = []
+    for pinned in (False, True):
+        g = ekf_slam_b200.EkfBatch(B, n_landmarks=N)
+        rr = np.random.default_rng(11)
+        outs = []
+        for s in range(5):
+            p = synth.batch_pose(B, s)
+            xy, _ = synth.batch_scan(fields, p, rr, m=N if s < 2 else m)
+            if pinned:
+                tp, tx = torch.from_numpy(p).pin_memory(), torch.from_numpy(xy).pin_memory()
+                ta = torch.empty((B, xy.shape[1]), dtype=torch.int32).pin_memory()
+                tc = torch.empty((B,), dtype=torch.int32).pin_memory()
+                tq = torch.empty((B, 3), dtype=torch.float64).pin_memory()
+                a, c, q = g.step(tp.numpy(), tx.numpy(), out=(ta.numpy(), tc.numpy(), tq.numpy()))
+                outs.append((a.copy(), c.copy(), q.copy()))
+            else:
+                outs.append(g.step(p, xy))
+        runs.append((outs, g.state(7), g.sigma(7)))
+        g.close()
+    for (a0, c0, q0), (a1, c1, q1) in zip(runs[0][0], runs[1][0]):
+        assert np.array_equal(a0, a1) and np.array_equal(c0, c1) and np.array_equal(q0, q1)
+    assert np.array_equal(runs[0][1], runs[1][1]) and np.array_equal(runs[0][2], runs[1][2])
+    assert int(runs[0][0][-1][1].min()) == N
