@@ -287,7 +287,8 @@ def bench_batched(args, torch, ekf, stream, local, world, dist):
     t_p = torch.empty((B, 3), dtype=torch.float64).pin_memory()
     out = (t_a.numpy(), t_c.numpy(), t_p.numpy())
     # (the filters are in steady state - all landmarks mapped - so a sighting set may be replayed as warm-up)
-    for s in range(W + K, W + K + 3):
+    for i in range(3):
+        s = W + K + (i % K)
         g.step(p_in[s][0], p_in[s][1], out=out)
     barrier()
     t0 = time.perf_counter()
