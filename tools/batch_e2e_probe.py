@@ -1,5 +1,6 @@
-import sys, time, numpy as np, torch
-sys.path.insert(0, "/root/repo")
+"""End-to-end cost of ekf_batch_step per route: pageable arrays (staged) vs page-locked arrays (copied directly)."""
+import os, sys, time, numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ekf_slam_b200 as ekf
 from ekf_slam_b200 import synth
 B, N, m = 65536, 20, 20
