@@ -96,6 +96,7 @@ struct ekf_filter {
   // second stream while the sequential side of scan s+1 runs on `stream`
   bool overlap = false;          // requested
   bool pipe_active = false;      // rounds issued since the last drain
+  bool pipe_ready = false;       // every allocation of the mode is in place
   double *sigma2 = nullptr;      // the other covariance buffer (pass k reads buffer k & 1, writes the other)
   double *W2 = nullptr, *V2 = nullptr;   // the other panel pair (round k writes / pass k reads pair k & 1)
   cudaStream_t back_stream = nullptr;

@@ -53,8 +53,20 @@ int pipe_drain(ekf_filter *f) {
 }
 
 // Allocations of the overlapped mode (second covariance buffer, second panel pair, stream, events).
+void pipe_release(ekf_filter *f);
+
+int pipe_resources_alloc(ekf_filter *f);
+
+// idempotent; a partial failure releases what it had got, so that a later call starts from scratch
 int pipe_resources(ekf_filter *f) {
-  if (f->sigma2) return EKF_OK;
+  if (f->pipe_ready) return EKF_OK;
+  const int rc = pipe_resources_alloc(f);
+  if (rc != EKF_OK) { pipe_release(f); return rc; }
+  f->pipe_ready = true;
+  return EKF_OK;
+}
+
+int pipe_resources_alloc(ekf_filter *f) {
   const size_t panel_bytes = (size_t)f->n_pad * f->kmax * sizeof(double);
   cudaError_t e = cudaMalloc(&f->sigma2, (size_t)f->sigma_elems * sizeof(double));
   if (e != cudaSuccess) { cudaGetLastError(); f->sigma2 = nullptr; return EKF_ERR_NOMEM; }
@@ -101,6 +113,9 @@ void pipe_release(ekf_filter *f) {
   if (f->done_host) cudaFreeHost(f->done_host);
   if (f->back_stream) cudaStreamDestroy(f->back_stream);
   f->sigma2 = nullptr; f->W2 = nullptr; f->V2 = nullptr; f->back_stream = nullptr; f->done_host = nullptr;
+  f->done_event = nullptr;
+  for (int q = 0; q < 2; ++q) { f->ev_seq[q] = nullptr; f->ev_pass[q] = nullptr; }
+  f->pipe_ready = false;
 }
 
 }  // namespace
