@@ -187,3 +187,40 @@ def test_replay_from_the_bag_equals_direct_replay(tmp_path):
                     for k, _, p in events if k != "junk")
     assert from_bag[0] == direct[0] and len(direct[0]) == 40
     assert np.array_equal(from_bag[1], direct[1]) and np.array_equal(from_bag[2], direct[2])
+
+
+def test_corrupted_files_are_rejected_or_read_never_crash(tmp_path):
+    """Bit flips, overwritten words and truncations of a good file (chunked + zstd when available, and unchunked):
+    the reader either returns a consistent bag or reports EKF_ERR_IO / EKF_ERR_NOMEM - it never faults."""
+    _, events = _trace(n_scans=6)
+    comp = "zstd" if mw.compression_available("zstd") else ""
+    good = tmp_path / "good.mcap"
+    mw.write_mcap(good, CHANNELS, _messages(events), chunk_messages=16, compression=comp)
+    raw_a = open(good, "rb").read()
+    mw.write_mcap(good, CHANNELS, _messages(events), chunk_messages=0)
+    raw_b = open(good, "rb").read()
+    rng = np.random.default_rng(0)
+    read = rejected = 0
+    path = tmp_path / "fuzzed.mcap"
+    for it in range(300):
+        b = bytearray(raw_a if it % 2 else raw_b)
+        if it % 3 == 0:
+            for _ in range(int(rng.integers(1, 6))):
+                b[int(rng.integers(8, len(b)))] = int(rng.integers(0, 256))
+        elif it % 3 == 1:
+            b = b[: int(rng.integers(9, len(b)))]
+        else:
+            p = int(rng.integers(8, len(b) - 8))
+            b[p:p + 8] = rng.integers(0, 256, 8, dtype=np.uint8).tobytes()
+        path.write_bytes(bytes(b))
+        try:
+            r = bag_mod.BagReader(path)
+        except bag_mod.BagError:
+            rejected += 1
+            continue
+        for e in range(r.n_events):
+            kind, index, _ = r.event(e)
+            (r.joint_state if kind == bag_mod.JOINT_STATE else r.detections)(index)
+        r.close()
+        read += 1
+    assert read + rejected == 300 and rejected > 50
