@@ -1,13 +1,15 @@
 #!/usr/bin/env python
-"""Generates the golden input/output vectors of the EKF hot path with oracle A (oracle/ekf_literal.py,
-the dense line-by-line restatement of nuslam/src/slam.cpp:180-316 and :318-530).
+"""Generates the golden input/output vectors of the EKF hot path FROM THE REFERENCE'S OWN SOURCE:
+oracle/_ref/libslam_ref.so is /root/reference/nuslam/src/slam.cpp compiled unmodified (oracle/Makefile,
+oracle/slam_ref_shim.cpp, stub ROS / Armadillo headers under oracle/stubs/); this script drives its
+Slam::fake_sensor_cb (slam.cpp:180-316) and Slam::sensor_cb (:318-530) and records what they leave in
+the node's members.
 
-    python tests/golden/make_golden.py        # rewrites tests/golden/*.npz
+    python tests/golden/make_golden.py        # rewrites tests/golden/*.npz (needs /root/reference)
 
-The reference itself cannot produce them (slam.cpp needs Armadillo + rclcpp, absent here; nuslam ships
-no test vectors): PARITY UNPINNED with respect to reference outputs.  The fixtures pin the restatement so
-that oracle B, the numpy models and the CUDA path are all held to the same numbers, and so that a later
-change of any of them shows up as a diff against committed data.
+nuslam ships no test vectors of its own (nuslam/CMakeLists.txt:37-47 is lint only), so these are the
+pins: oracle A, oracle B, the numpy models and the CUDA path are all held to them.  The reference tree
+does not exist on the GPU box, which is why the vectors are committed.
 
 Each file holds: the inputs (per scan: composed odometry (x, y, theta) as the node shell passes it,
 body-frame sightings, ids, action flags, ragged via `m`), and the outputs (association per sighting,
@@ -22,7 +24,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")]
 
-import ekf_literal as lit  # noqa: E402
+import slam_ref  # noqa: E402
 from ekf_slam_b200 import synth  # noqa: E402
 
 CASES = {
@@ -45,7 +47,7 @@ def generate(name, known, N, kw, field=None):
     odom = np.zeros((S, 3)); m = np.zeros(S, dtype=np.int32)
     xy = np.zeros((S, mmax, 2)); ids = np.full((S, mmax), -1, dtype=np.int32); act = np.zeros((S, mmax), dtype=np.uint8)
     assoc = np.full((S, mmax), -1, dtype=np.int32); poses = np.zeros((S, 3))
-    f = lit.LiteralEkf(n_landmarks=N)
+    f = slam_ref.RefSlam(n_landmarks=N, sensor_source="sim" if known else "assoc")
     for i, s in enumerate(scans):
         k = len(s.xy)
         odom[i] = s.odom; m[i] = k
@@ -59,7 +61,8 @@ def generate(name, known, N, kw, field=None):
         poses[i] = f.state[:3]
     np.savez_compressed(os.path.join(HERE, name + ".npz"), known=known, n_landmarks=N, odom=odom, m=m, xy=xy, ids=ids,
                         action=act, assoc=assoc, poses=poses, state=f.state.copy(), sigma=f.sigma.copy(),
-                        count=f.counter_obstacles)
+                        count=f.counter_obstacles, t_map_odom=f.t_map_odom, source="reference slam.cpp via oracle/_ref")
+    assert f.second_branch_taken == 0   # slam.cpp:423-432 is unreachable
     print(name, "scans", S, "max m", mmax, "count", f.counter_obstacles)
 
 

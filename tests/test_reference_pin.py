@@ -1,0 +1,295 @@
+"""Pins the oracles to the REFERENCE'S OWN EKF SOURCE.
+
+oracle/_ref/libslam_ref.so is /root/reference/nuslam/src/slam.cpp compiled unmodified (oracle/Makefile,
+oracle/slam_ref_shim.cpp, stub headers under oracle/stubs/): Slam::fake_sensor_cb (slam.cpp:180-316),
+Slam::sensor_cb (:318-530), Slam::jointStateCallback (:599-634) and the constructor's filter set-up
+(:127-139) run as the reference wrote them.  Every oracle and model used by the GPU parity tests is
+compared with it here: association identical, state <= 1e-9, Sigma <= 1e-9 norm-wise (whole matrix) and
+the observed block at the reference's own 1e7-prior cancellation floor (<= 1e-6).
+
+The library is built in this container (the reference tree does not exist on the GPU box; the prebuilt
+file travels there).  Tests skip only when it is genuinely absent.
+"""
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from _harness import rel_fro, run_literal, run_model, run_struct, synth
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+import ekf_literal as lit  # noqa: E402
+import slam_ref  # noqa: E402
+
+pytestmark = pytest.mark.skipif(not slam_ref.available(), reason="oracle/_ref/libslam_ref.so not built")
+
+STATE_TOL = 1e-9
+SIGMA_TOL = 1e-9
+ACTIVE_TOL = 1e-6
+
+
+def run_reference(scans, known, n_landmarks=50, **kw):
+    f = slam_ref.RefSlam(n_landmarks=n_landmarks, sensor_source="sim" if known else "assoc", **kw)
+    assoc = []
+    for s in scans:
+        f.set_odometry(*s.odom)
+        if known:
+            f.fake_sensor_cb([(int(i), x, y, int(a)) for i, (x, y), a in zip(s.ids, s.xy, s.action)])
+            assoc.append(list(s.ids))
+        elif len(s.xy):
+            assoc.append(f.sensor_cb([(x, y) for (x, y) in s.xy]))
+        else:
+            assoc.append([])
+    assert f.second_branch_taken == 0       # slam.cpp:423-432 never runs
+    return assoc, f.state, f.sigma, f.counter_obstacles, f
+
+
+def _active(state):
+    idx = [0, 1, 2] + [int(i) for i in np.nonzero(state[3:])[0] + 3]
+    return np.ix_(idx, idx)
+
+
+def _same(ref, got, known):
+    ra, rs, rS, rc = ref[:4]
+    ga, gs, gS, gc = got[:4]
+    if not known:
+        assert [list(a) for a in ra] == [list(a) for a in ga]
+        assert rc == gc
+    assert rel_fro(gs, rs) <= STATE_TOL
+    assert rel_fro(gS, rS) <= SIGMA_TOL
+    blk = _active(rs)
+    assert rel_fro(gS[blk], rS[blk]) <= ACTIVE_TOL
+
+
+TRACES = {
+    "config1_known": dict(known=True, N=50, kw=dict(n_scans=80, seed=0, max_range=1.2)),
+    "config1_known_all_in_range": dict(known=True, N=50, kw=dict(n_scans=40, seed=3)),
+    "config2_unknown": dict(known=False, N=50, kw=dict(n_scans=80, seed=1, drop_out_of_range=True, shuffle=True)),
+    "config2_unknown_noisy": dict(known=False, N=50, kw=dict(n_scans=40, seed=7, drop_out_of_range=True, shuffle=True,
+                                                              sensor_std=0.01, slip=0.3)),
+    "config3_n43": dict(known=False, N=20, field=(20, 21), kw=dict(n_scans=25, seed=5, drop_out_of_range=True,
+                                                                     shuffle=True, max_range=1.8)),
+    "twelve_in_fifty": dict(known=False, N=50, field=(12, 4), kw=dict(n_scans=30, seed=9, drop_out_of_range=True,
+                                                                       shuffle=True, max_range=1.5)),
+}
+
+
+def _scans(c):
+    kw = dict(c["kw"])
+    if "field" in c:
+        kw["landmarks"] = synth.scattered_field(c["field"][0], seed=c["field"][1], extent=4.0, min_sep=0.5)
+    return synth.circle_drive(**kw)
+
+
+@pytest.mark.parametrize("name", sorted(TRACES))
+def test_oracle_a_equals_reference_source(name):
+    c = TRACES[name]
+    scans = [s for s in _scans(c) if c["known"] or len(s.xy)]
+    ref = run_reference(scans, c["known"], c["N"])
+    _same(ref, run_literal(scans, c["known"], c["N"]), c["known"])
+
+
+@pytest.mark.parametrize("name", sorted(TRACES))
+def test_oracle_b_and_gpu_model_equal_reference_source(name):
+    c = TRACES[name]
+    scans = [s for s in _scans(c) if c["known"] or len(s.xy)]
+    ref = run_reference(scans, c["known"], c["N"])
+    _same(ref, run_struct(scans, c["known"], c["N"]), c["known"])
+    _same(ref, run_model(scans, c["known"], c["N"]), c["known"])
+
+
+def test_reference_constructor_matches_documented_defaults():
+    """slam.cpp:127-139,665-671: Sigma0 = diag(0,0,0, 1e7 I), state 0, threshold 2.0, N = 50."""
+    f = slam_ref.RefSlam()
+    assert f.n == 103 and f.counter_obstacles == 0
+    S = f.sigma
+    assert np.array_equal(S, np.diag([0.0] * 3 + [10e6] * 100))
+    assert not f.state.any()
+    assert slam_ref.lib().slam_ref_threshold(f._h) == 2.0
+    a = lit.LiteralEkf()
+    assert np.array_equal(a.sigma, S) and a.mah_threshold == 2.0
+
+
+def test_capacity_hook_changes_only_the_size():
+    """the shim's construction hook sets n_landmarks (slam.cpp:665) before the matrices are sized"""
+    for N in (4, 20, 120):
+        f = slam_ref.RefSlam(n_landmarks=N)
+        n = 2 * N + 3
+        assert f.n == n and f.sigma.shape == (n, n) and f.state.shape == (n,)
+        assert np.array_equal(f.sigma, np.diag([0.0] * 3 + [10e6] * (2 * N)))
+
+
+def test_larger_capacity_n243_against_reference_source():
+    """N = 120 (n = 243): a map larger than the reference ships, still its own code path"""
+    field = synth.scattered_field(40, seed=2, extent=5.0, min_sep=0.45)
+    scans = [s for s in synth.circle_drive(n_scans=12, seed=2, landmarks=field, drop_out_of_range=True, shuffle=True,
+                                           max_range=2.2) if len(s.xy)]
+    ref = run_reference(scans, False, 120)
+    _same(ref, run_literal(scans, False, 120), False)
+    _same(ref, run_struct(scans, False, 120), False)
+    _same(ref, run_model(scans, False, 120), False)
+
+
+def test_non_default_noise_and_threshold():
+    scans = [s for s in synth.circle_drive(n_scans=30, seed=11, drop_out_of_range=True, shuffle=True, sensor_std=0.02)
+             if len(s.xy)]
+    kw = dict(q_noise=3e-3, r_noise=5e-2, mah_threshold=3.5)
+    ref = run_reference(scans, False, 50, **kw)
+    _same(ref, run_literal(scans, False, 50, **kw), False)
+    _same(ref, run_struct(scans, False, 50, **kw), False)
+
+
+def test_wheel_odometry_through_joint_state_callback():
+    """Slam::jointStateCallback (slam.cpp:599-634) -> DiffDrive::FKin: the reference's t_odom_robot from
+    the encoder angles equals oracle A's DiffDrive bit for bit, and the filter run on it matches."""
+    scans = [s for s in synth.circle_drive(n_scans=25, seed=4, drop_out_of_range=True, shuffle=True) if len(s.xy)]
+    f = slam_ref.RefSlam(sensor_source="assoc")
+    a = lit.LiteralEkf()
+    dd = lit.DiffDrive(synth.TRACK_WIDTH, synth.WHEEL_RADIUS)
+    for s in scans:
+        f.joint_state(*s.wheels)
+        t = dd.fkin(*s.wheels)
+        assert tuple(f.t_odom_robot) == (t.x, t.y, t.rot)
+        a.set_odometry(t.x, t.y, t.rot)
+        assert f.sensor_cb([(x, y) for (x, y) in s.xy]) == a.sensor_cb([(x, y) for (x, y) in s.xy])
+    assert rel_fro(a.state, f.state) <= STATE_TOL
+    assert rel_fro(a.sigma, f.sigma) <= SIGMA_TOL
+    tmo = np.array([a.t_map_odom.x, a.t_map_odom.y, a.t_map_odom.rot])
+    assert np.abs(tmo - f.t_map_odom).max() <= 1e-9
+
+
+def test_published_tf_and_markers_are_the_filter_outputs():
+    """slam.cpp:281-289,512-528: the tf carries t_map_odom, green/obstacles carries the map estimate"""
+    scans = [s for s in synth.circle_drive(n_scans=10, seed=6, drop_out_of_range=True) if len(s.xy)]
+    _, state, _, count, f = run_reference(scans, False)
+    x, y, th = f.t_map_odom
+    assert np.allclose(f.last_tf(), [x, y, math.sin(th / 2.0), math.cos(th / 2.0)], rtol=0, atol=0)
+    ids, xy = f.published_markers()
+    assert list(ids) == list(range(count))
+    assert np.array_equal(xy.reshape(-1), state[3:3 + 2 * count])
+
+
+def test_capacity_overflow_is_the_reference_bounds_error():
+    """51st landmark: state(3 + 2*50) is out of bounds (slam.cpp:351 with :665) -> std::out_of_range from the
+    element access; oracle A raises IndexError at the same measurement; the C ABI's EKF_ERR_CAPACITY mirrors it."""
+    N = 6
+    field = synth.scattered_field(10, seed=8, extent=3.0, min_sep=0.6)
+    scans = [s for s in synth.circle_drive(n_scans=6, seed=8, landmarks=field, drop_out_of_range=True, max_range=3.0)
+             if len(s.xy)]
+    f = slam_ref.RefSlam(n_landmarks=N)
+    a = lit.LiteralEkf(n_landmarks=N)
+    f.set_odometry(*scans[0].odom)
+    a.set_odometry(*scans[0].odom)
+    xy = [(x, y) for (x, y) in scans[0].xy]
+    assert len(xy) > N
+    with pytest.raises(slam_ref.RefOutOfRange):
+        f.sensor_cb(xy)
+    with pytest.raises(IndexError):
+        a.sensor_cb(xy)
+    # both stopped at the 7th sighting with the first six fused
+    assert f.counter_obstacles == N == a.counter_obstacles
+    assert rel_fro(a.state, f.state) <= STATE_TOL
+
+
+def test_empty_scan_throws_after_predicting():
+    """an empty MarkerArray reaches msg.markers.at(0) (slam.cpp:498): std::out_of_range, after the prediction
+    and the t_map_odom update ran but before filter_previous_configuration moved (:508)"""
+    f = slam_ref.RefSlam()
+    f.set_odometry(0.3, -0.1, 0.2)
+    before = f.sigma
+    with pytest.raises(slam_ref.RefOutOfRange):
+        f.sensor_cb([])
+    after = f.sigma
+    assert after[0, 0] == before[0, 0] + 1e-2 and after[1, 1] == 1e-2
+
+
+def test_exact_ties_go_to_the_lowest_index():
+    """two landmarks that are mirror images about the robot's heading axis with a sighting on the axis have
+    bit-identical Mahalanobis distances when their covariances mirror too: index_min (slam.cpp:418) takes the
+    first.  Built by fixture injection (set_state / set_sigma) on the reference, oracle A and oracle B."""
+    import struct_oracle as so
+    N = 6
+    n = 2 * N + 3
+    state = np.zeros(n)
+    state[3:7] = [1.0, 0.25, 1.0, -0.25]            # landmark 0 at (1, .25), landmark 1 at (1, -.25)
+    sig = np.zeros((n, n))
+    sig[np.arange(3, n), np.arange(3, n)] = 10e6
+    sig[0, 0] = 1e-3; sig[1, 1] = 2e-3; sig[2, 2] = 2e-3
+    for k in (0, 1):
+        sig[3 + 2 * k, 3 + 2 * k] = 0.5; sig[4 + 2 * k, 4 + 2 * k] = 0.5
+    thr = 50.0                                       # wide gate so the tie is inside it
+    f = slam_ref.RefSlam(n_landmarks=N, mah_threshold=thr)
+    f.set_state(state, 2); f.set_sigma(sig)
+    a = lit.LiteralEkf(n_landmarks=N, mah_threshold=thr)
+    a.state[:] = state; a.sigma[:] = sig; a.counter_obstacles = 2
+    b = so.StructEkf(n_landmarks=N, mah_threshold=thr)
+    b.state[:] = state; b.sigma[:] = sig; b.count = 2
+    got_ref = f.sensor_cb([(1.0, 0.0)])
+    got_a = a.sensor_cb([(1.0, 0.0)])
+    b.predict(0.0, 0.0, 0.0)
+    got_b = list(b.update_unknown(np.array([[1.0, 0.0]])))
+    assert got_ref == [0] and got_a == [0] and got_b == [0]
+    b.close()
+
+
+def test_landmark_on_top_of_the_robot_nan_never_wins():
+    """d = 0 -> H has inf/NaN entries -> NaN distance (slam.cpp:384-401); index_min's strict '<' never
+    selects it, so the sighting opens a new landmark.  Reference, oracle A and oracle B agree."""
+    import struct_oracle as so
+    N = 6
+    n = 2 * N + 3
+    state = np.zeros(n)
+    state[1] = 0.5; state[2] = 0.5
+    state[3:5] = [0.5, 0.5]                          # landmark 0 exactly at the robot position
+    sig = np.diag([1e-2] * 3 + [0.1, 0.1] + [10e6] * (n - 5))
+    f = slam_ref.RefSlam(n_landmarks=N)
+    f.set_state(state, 1); f.set_sigma(sig)
+    f.set_odometry(0.5, 0.5, 0.0); f.set_previous(0.5, 0.5)
+    a = lit.LiteralEkf(n_landmarks=N)
+    a.state[:] = state; a.sigma[:] = sig; a.counter_obstacles = 1
+    a.set_odometry(0.5, 0.5, 0.0); a.filter_previous_configuration = lit.Transform2D(0.5, 0.5, 0.0)
+    with np.errstate(all="ignore"):
+        got_a = a.sensor_cb([(0.7, 0.1)])
+    got_ref = f.sensor_cb([(0.7, 0.1)])
+    b = so.StructEkf(n_landmarks=N)
+    b.state[:] = state; b.sigma[:] = sig; b.count = 1; b.set_prev(0.5, 0.5)
+    b.predict(0.0, 0.5, 0.5)
+    got_b = list(b.update_unknown(np.array([[0.7, 0.1]])))
+    assert got_ref == [1] and got_a == [1] and got_b == [1]
+    assert f.counter_obstacles == 2 == a.counter_obstacles == b.count
+    b.close()
+
+
+# ------------------------------------------------------------------------------------------------
+# the CUDA path against the reference's object code (the prebuilt oracle/_ref travels to the GPU box)
+@pytest.mark.gpu
+@pytest.mark.parametrize("fused", [False, True], ids=["split_calls", "ekf_scan"])
+@pytest.mark.parametrize("name", sorted(TRACES))
+def test_cuda_equals_reference_source(name, fused):
+    from _harness import run_gpu
+    c = TRACES[name]
+    scans = [s for s in _scans(c) if c["known"] or len(s.xy)]
+    ref = run_reference(scans, c["known"], c["N"])
+    _same(ref, run_gpu(scans, c["known"], c["N"], fused=fused), c["known"])
+
+
+@pytest.mark.gpu
+def test_cuda_larger_capacity_n243_equals_reference_source():
+    from _harness import run_gpu
+    field = synth.scattered_field(40, seed=2, extent=5.0, min_sep=0.45)
+    scans = [s for s in synth.circle_drive(n_scans=12, seed=2, landmarks=field, drop_out_of_range=True, shuffle=True,
+                                           max_range=2.2) if len(s.xy)]
+    ref = run_reference(scans, False, 120)
+    _same(ref, run_gpu(scans, False, 120, fused=True), False)
+
+
+@pytest.mark.gpu
+def test_cuda_non_default_noise_equals_reference_source():
+    from _harness import run_gpu
+    scans = [s for s in synth.circle_drive(n_scans=30, seed=11, drop_out_of_range=True, shuffle=True, sensor_std=0.02)
+             if len(s.xy)]
+    kw = dict(q_noise=3e-3, r_noise=5e-2, mah_threshold=3.5)
+    ref = run_reference(scans, False, 50, **kw)
+    _same(ref, run_gpu(scans, False, 50, fused=True, **kw), False)
