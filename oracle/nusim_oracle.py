@@ -11,11 +11,15 @@ Follows, expression by expression:
   tf2 Quaternion::setRPY / getAngle (third-party, absent from /root/reference; the published formulas:
   setRPY(0,0,yaw) = (0, 0, sin(yaw/2), cos(yaw/2)), getAngle() = 2 acos(clamp(w, -1, 1)))
 
-PARITY UNPINNED for the sensor models themselves: the reference has no test or golden vector for nusim,
-and nusim.cpp needs rclcpp / tf2 to compile.  The SE(2) algebra underneath IS pinned, bit for bit,
-against the reference's own turtlelib compiled from /root/reference (tests/test_nusim.py, oracle/_ref).
+PINNED against the reference's own object code: oracle/_ref/libnusim_ref.so is nusim/src/nusim.cpp
+compiled unmodified (oracle/Makefile, oracle/nusim_ref_shim.cpp, stub ROS headers under oracle/stubs/);
+tests/test_nusim.py holds this restatement to it BIT FOR BIT (lidar ranges, fake-sensor coordinates, ids
+and ADD/DELETE flags, wall markers), with and without noise.  The SE(2) algebra underneath is also
+pinned against the reference's turtlelib (oracle/_ref/libturtlelib_ref.so).
 The random draws (std::normal_distribution over mt19937, nusim.cpp:202,341-342,706) are an input here:
-`noise` arrays are added where the reference adds `sensor_normal_dist(gen)`.
+`noise` arrays are added where the reference adds `sensor_normal_dist(gen)`.  Draw order in the
+reference binary (g++ evaluates the two noisy create_obstacle arguments right to left): per sensor tick
+360 lidar draws in beam order, then per obstacle the Y draw before the X draw.
 """
 from __future__ import annotations
 

@@ -9,6 +9,7 @@
 #define ORACLE_STUB_ROS_CORE_HPP
 #include <array>
 #include <chrono>
+#include <cmath>
 #include <cstdint>
 #include <functional>
 #include <map>
@@ -103,7 +104,24 @@ public:
   Quaternion() = default;
   Quaternion(double x, double y, double z, double w)
   : x_(x), y_(y), z_(z), w_(w) {}
-  void setRPY(double roll, double pitch, double yaw);
+  // tf2/LinearMath/Quaternion.h (third-party, absent here): the published formulas
+  void setRPY(double roll, double pitch, double yaw)
+  {
+    const double hy = yaw * 0.5, hp = pitch * 0.5, hr = roll * 0.5;
+    const double cy = std::cos(hy), sy = std::sin(hy), cp = std::cos(hp), sp = std::sin(hp);
+    const double cr = std::cos(hr), sr = std::sin(hr);
+    x_ = sr * cp * cy - cr * sp * sy;
+    y_ = cr * sp * cy + sr * cp * sy;
+    z_ = cr * cp * sy - sr * sp * cy;
+    w_ = cr * cp * cy + sr * sp * sy;
+  }
+  double getAngle() const
+  {
+    double w = w_;
+    if (w < -1.0) {w = -1.0;}
+    if (w > 1.0) {w = 1.0;}
+    return 2.0 * std::acos(w);
+  }
   double x() const {return x_;}
   double y() const {return y_;}
   double z() const {return z_;}

@@ -72,6 +72,59 @@ def test_oracle_lidar_feeds_landmark_extraction():
         assert np.min(np.hypot(truth[:, 0] - d[0], truth[:, 1] - d[1])) < 0.02 and abs(d[2] - 0.05) < 0.02
 
 
+# ---------------------------------------------------------------- CPU: oracle == the reference's nusim.cpp
+def _ref_or_skip():
+    import nusim_ref
+    if not nusim_ref.available():
+        pytest.skip("oracle/_ref/libnusim_ref.so not built (reference tree absent)")
+    return nusim_ref
+
+
+def test_oracle_equals_reference_nusim_source_noise_free():
+    """NuSim::sensor_timer_callback / publish_lidar_data run from the reference's own object code
+    (nusim.cpp:310-349, 559-710): every lidar range, sighting coordinate, id and ADD/DELETE flag is
+    bit-identical to the restatement."""
+    nr = _ref_or_skip()
+    rng = np.random.default_rng(0)
+    for world, arena, rmax in [(OBST, (ARENA_X, ARENA_Y), MAX_RANGE), (OBST, (ARENA_X, ARENA_Y), 1.0),
+                               (np.array([[1.0, 0.0, 0.3], [0.05, 0.0, 0.05], [-2.0, 1.0, 0.1]]), (6.0, 6.0), 3.0)]:
+        f = nr.RefNuSim(world, arena[0], arena[1], max_range=rmax)
+        walls = f.walls()
+        for (px, py, sx, ang), w in zip(no.wall_markers(*arena), walls):
+            assert (px, py, sx) == tuple(w[:3])
+            assert ang == 2.0 * math.acos(max(-1.0, min(1.0, w[4])))
+        for _ in range(40):
+            pose = (rng.uniform(-math.pi, math.pi), rng.uniform(-1.5, 1.5), rng.uniform(-1.2, 1.2))
+            f.set_pose(*pose)
+            ranges, xy, ids, act = f.sensor_tick()
+            assert np.array_equal(ranges, no.lidar(pose, world, arena[0], arena[1], rmax))
+            xyo, ido = no.fake_sensor(pose, world[:, :2], rmax)
+            assert np.array_equal(xy, xyo)
+            assert list(ids) == list(range(len(world)))
+            assert [int(a) == 2 for a in act] == [int(i) < 0 for i in ido]      # Marker::DELETE beyond max_range
+
+
+def test_oracle_equals_reference_nusim_source_with_noise():
+    """the same with sensor noise on: the reference's draws (libstdc++ normal_distribution over mt19937) fed
+    to the restatement in the reference's draw order reproduce its output bit for bit"""
+    nr = _ref_or_skip()
+    std = 0.001                                   # nusim.cpp:88 default
+    f = nr.RefNuSim(OBST, ARENA_X, ARENA_Y, max_range=1.2, sensor_std=std, seed=5)
+    rng = np.random.default_rng(1)
+    ticks = 6
+    draws = nr.normal_draws(5, std, ticks * (360 + 2 * len(OBST)))
+    for t in range(ticks):
+        pose = (rng.uniform(-math.pi, math.pi), rng.uniform(-0.5, 0.5), rng.uniform(-0.5, 0.5))
+        f.set_pose(*pose)
+        d = draws[t * (360 + 2 * len(OBST)):(t + 1) * (360 + 2 * len(OBST))]
+        ranges, xy, ids, act = f.sensor_tick()
+        assert np.array_equal(ranges, no.lidar(pose, OBST, ARENA_X, ARENA_Y, 1.2, noise=d[:360]))
+        yx = d[360:].reshape(-1, 2)               # Y is drawn before X
+        xyo, ido = no.fake_sensor(pose, OBST[:, :2], 1.2, noise=yx[:, ::-1])
+        assert np.array_equal(xy, xyo)
+        assert [int(a) == 2 for a in act] == [int(i) < 0 for i in ido]
+
+
 # ---------------------------------------------------------------- GPU: the device generators
 def _poses(n, seed):
     rng = np.random.default_rng(seed)
