@@ -16,7 +16,9 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libekf_slam_b200.so")
+# EKF_SLAM_B200_LIB selects another build of the same library for A/B measurements (tools/near_tie_probe.py:
+# the FMA-free association variant).  It must be a library built from this tree; there is no other backend.
+LIB_PATH = os.environ.get("EKF_SLAM_B200_LIB") or os.path.join(_HERE, "libekf_slam_b200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "ekf_slam_b200.h")
 
 EKF_OK, EKF_ERR_INVALID, EKF_ERR_CAPACITY, EKF_ERR_EMPTY_SCAN, EKF_ERR_BAD_ID, EKF_ERR_CUDA, \
@@ -97,6 +99,7 @@ def load() -> C.CDLL:
         "ekf_get_previous_xy": (C.c_int, [vp, dp]),
         "ekf_set_sigma_block": (C.c_int, [vp, i32, i32, i32, i32, dp]),
         "ekf_fill_procedural": (C.c_int, [vp, C.c_uint64, i32, i32]),
+        "ekf_mahalanobis": (C.c_int, [vp, C.c_double, C.c_double, dp, i32, C.POINTER(i32)]),
         "ekf_sigma_storage": (C.c_int, [vp, i64p, i64p]),
         "ekf_launch_count": (C.c_int, [vp, i64p]),
         "ekf_read_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),
@@ -342,6 +345,14 @@ class EkfSlam:
         out = np.zeros(2)
         self._check(self._L.ekf_get_previous_xy(self._h, _dp(out)), "ekf_get_previous_xy")
         return out
+
+    def mahalanobis(self, x: float, y: float) -> np.ndarray:
+        """distances of the body-frame sighting (x, y) to every mapped landmark (slam.cpp:358-404), read-only"""
+        out = np.zeros(max(self.n_landmarks, 1))
+        c = C.c_int32(0)
+        self._check(self._L.ekf_mahalanobis(self._h, float(x), float(y), _dp(out), self.n_landmarks, C.byref(c)),
+                    "ekf_mahalanobis")
+        return out[:c.value].copy()
 
     def fill_procedural(self, seed: int, count: int, grid_w: int):
         self._check(self._L.ekf_fill_procedural(self._h, C.c_uint64(seed), count, grid_w), "ekf_fill_procedural")

@@ -139,6 +139,28 @@ int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
   return EKF_OK;
 }
 
+int ekf_mahalanobis(ekf_filter *f, double x, double y, double *out_d, int32_t cap, int32_t *count) {
+  if (!f || !out_d || cap < 0) return EKF_ERR_INVALID;
+  if (f->sharded) return EKF_ERR_INVALID;   // a row shard does not hold every block the sweep reads
+  int32_t c = 0;
+  int rc = ekf_get_count(f, &c);            // (synchronises the stream; drains nothing else)
+  if (rc != EKF_OK) return rc;
+  if (count) *count = c;
+  const int32_t k = c < cap ? c : cap;
+  if (k == 0) return EKF_OK;
+  DeviceGuard guard(f->device);
+  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
+  rc = ensure_scratch(f, (size_t)k * 8);
+  if (rc != EKF_OK) return rc;
+  mahalanobis_sweep_kernel<<<(k + 127) / 128, 128, 0, f->stream>>>(f->sigma, f->lay, f->mu, f->cnt, x, y,
+                                                                  f->cfg.r_noise, f->scratch_dev, k);
+  f->launches++;
+  CK(f, cudaGetLastError());
+  CK(f, cudaMemcpyAsync(out_d, f->scratch_dev, (size_t)k * 8, cudaMemcpyDeviceToHost, f->stream));
+  CK(f, cudaStreamSynchronize(f->stream));
+  return EKF_OK;
+}
+
 int ekf_fill_procedural(ekf_filter *f, uint64_t seed, int32_t count, int32_t grid_w) {
   if (!f || count < 0 || count > f->N || grid_w < 1) return EKF_ERR_INVALID;
   f->side_valid = false;

@@ -6,6 +6,7 @@
 #include <stdint.h>
 
 #include "ekf_layout.h"
+#include "ekf_math.cuh"
 
 namespace ekf {
 
@@ -47,6 +48,33 @@ __global__ void state_to_ext_kernel(const double *mu, double *out, int n) {
 __global__ void state_from_ext_kernel(double *mu, const double *in, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) mu[ekf_int_index(i)] = in[i];
+}
+
+// Mahalanobis distance of ONE body-frame sighting to every mapped landmark against the filter as it stands:
+// the sweep of slam.cpp:358-404 without the tentative landmark, the decision or the update.  One thread per
+// landmark; the 5x5 block {theta, x, y, lx, ly}^2 comes straight from the stored triangle.  Same device
+// functions, in the same order, as phase A of ekf_seq_kernel - a diagnostic for the decision margins.
+__global__ void mahalanobis_sweep_kernel(const double *sigma, EkfLay lay, const double *mu, const int *cnt, double mx,
+                                         double my, double r_noise, double *out, int cap) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= *cnt || k >= cap) return;
+  double pb[3][3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j <= i; ++j) pb[i][j] = pb[j][i] = sigma[ekf_lay_elem(lay, i, j)];
+  const int a = 4 + 2 * k;
+  const double *ra = sigma + ekf_lay_elem(lay, a, 0), *rb = sigma + ekf_lay_elem(lay, a + 1, 0);
+  const double pa3[3] = {ra[0], ra[1], ra[2]}, pb3[3] = {rb[0], rb[1], rb[2]};
+  const double *dg = sigma + ekf_lay_elem(lay, a, a);
+  const Polar z = to_polar(mx, my);
+  const Lin L = linearize(mu[0], mu[1], mu[2], mu[a], mu[a + 1]);
+  const Block5 B = make_block5(pb, pa3, pb3, dg[0], dg[EKF_STRIP], dg[EKF_STRIP + 1]);
+  const Innov I = innovation(B, L, r_noise);
+  const double zd0 = z.r - L.zhat_r;
+  const double zd1 = normalize_angle(z.phi - L.zhat_b);
+  double i00, i01, i11;
+  out[k] = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
 }
 
 // ---- procedural fixture --------------------------------------------------------------------------

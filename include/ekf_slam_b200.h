@@ -142,6 +142,11 @@ int ekf_set_previous_xy(ekf_filter *f, double x, double y);   /* filter_previous
 int ekf_get_previous_xy(ekf_filter *f, double out[2]);
 /* writes the entries with row >= col of the given block into the stored triangle */
 int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32_t j1, const double *in);
+/* Association sweep alone (slam.cpp:358-404 without the tentative entry, the decision or the update):
+ * out_d[k] = Mahalanobis distance of the body-frame sighting (x, y) to mapped landmark k, k < min(count,
+ * cap), against the filter as it stands; *count = counter_obstacles.  Read-only.  This is how tests and
+ * bench.py log the decision margins (min |d - threshold|, best-vs-second gap) of a scan. */
+int ekf_mahalanobis(ekf_filter *f, double x, double y, double *out_d, int32_t cap, int32_t *count);
 /* Procedural large-map fixture: `count` landmarks on a jittered
  * unit grid of `grid_w` columns, state consistent with it, Sigma = block-diagonal SPD + a
  * rank-8 hash-generated cross term.  Deterministic in `seed`; generated on the device. */

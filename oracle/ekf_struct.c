@@ -296,7 +296,16 @@ static void assoc_body(long lo, long hi, void *vc) { /* slam.cpp:361-416, existi
  * matches an existing landmark, which this restatement allows so that a full map stays
  * usable (the tentative slot is then simply not materialised; its distance is the
  * threshold either way, slam.cpp:406-408). */
+int ekfo_update_unknown_ex(ekfo_t *f, int m, const double *xy, int *assoc, double *best_d, double *second_d);
 int ekfo_update_unknown(ekfo_t *f, int m, const double *xy, int *assoc) {
+  return ekfo_update_unknown_ex(f, m, xy, assoc, NULL, NULL);
+}
+
+/* The same, also reporting the decision margins: best_d[i] / second_d[i] = the smallest and
+ * second-smallest Mahalanobis distance of measurement i over the EXISTING landmarks (the tentative entry excluded;
+ * +inf when there are fewer).  A decision can only differ between two implementations when best_d is within their
+ * arithmetic difference of the threshold, or of second_d. */
+int ekfo_update_unknown_ex(ekfo_t *f, int m, const double *xy, int *assoc, double *best_d, double *second_d) {
   for (int i = 0; i < m; ++i) {
     const double mx = xy[2 * i], my = xy[2 * i + 1];
     const double z[2] = {sqrt(pow(mx, 2) + pow(my, 2)), atan2(my, mx)};
@@ -311,6 +320,15 @@ int ekfo_update_unknown(ekfo_t *f, int m, const double *xy, int *assoc) {
     assoc_ctx ac = {f, z};
     par_for((long)cnt, 64, assoc_body, &ac);
     dist[cnt] = f->thr; /* the tentative landmark: slam.cpp:406-408 */
+    if (best_d || second_d) {
+      double b1 = INFINITY, b2 = INFINITY;
+      for (int k = 0; k < cnt; ++k) {
+        if (dist[k] < b1) { b2 = b1; b1 = dist[k]; }
+        else if (dist[k] < b2) b2 = dist[k];
+      }
+      if (best_d) best_d[i] = b1;
+      if (second_d) second_d[i] = b2;
+    }
     /* arma::index_min: strict '<' from +inf, first minimum wins, NaN never selected */
     double best = INFINITY;
     int min_index = 0;

@@ -52,6 +52,7 @@ def lib():
             getattr(L, name).restype = None
         L.slam_ref_fake_sensor.argtypes = [vp, C.c_int, ip, dp, C.POINTER(C.c_ubyte)]
         L.slam_ref_sensor.argtypes = [vp, C.c_int, dp, ip, dp, ip]
+        L.slam_ref_sensor_ex.argtypes = [vp, C.c_int, dp, ip, dp, ip, dp, dp]
         L.slam_ref_set_state.argtypes = [vp, dp, C.c_int]
         L.slam_ref_set_previous.argtypes = [vp, C.c_double, C.c_double, C.c_double]
         L.slam_ref_set_map_odom.argtypes = [vp, C.c_double, C.c_double, C.c_double]
@@ -85,6 +86,7 @@ class RefSlam:
         self.n = self._L.slam_ref_n(self._h)
         self.second_branch_taken = 0
         self.last_min = []
+        self.last_best = self.last_second = np.zeros(0)
         if q_noise is not None or r_noise is not None or mah_threshold is not None:
             self._L.slam_ref_set_noise(self._h, 1e-2 if q_noise is None else q_noise,
                                        1e-2 if r_noise is None else r_noise,
@@ -129,9 +131,13 @@ class RefSlam:
         assoc = np.full(max(m, 1), -1, dtype=np.int32)
         dist = np.zeros(max(m, 1))
         second = C.c_int(0)
-        rc = self._L.slam_ref_sensor(self._h, m, _dp(xy), _ip(assoc), _dp(dist), C.byref(second))
+        best, second_d = np.zeros(max(m, 1)), np.zeros(max(m, 1))
+        rc = self._L.slam_ref_sensor_ex(self._h, m, _dp(xy), _ip(assoc), _dp(dist), C.byref(second), _dp(best),
+                                        _dp(second_d))
         self.second_branch_taken += second.value
         self.last_min = dist[:m].tolist()
+        self.last_best = best[:m].copy()          # smallest distance over the existing landmarks, per measurement
+        self.last_second = second_d[:m].copy()    # second smallest
         if rc:
             self._raise(rc)
         return assoc[:m].tolist()

@@ -162,7 +162,19 @@ int slam_ref_fake_sensor(SlamRef * h, int m, const int * ids, const double * xy,
 // the callback calls index_min then min (:418-419) and, in the branch at :423-432 only,
 // index_min once more.  out_assoc[i] = the min_index used at :443; out_dist[i] = the value
 // `min` (:419); *out_second_branch counts how often the :423 branch ran (it is unreachable).
+int slam_ref_sensor_ex(
+  SlamRef * h, int m, const double * xy, int * out_assoc, double * out_dist, int * out_second_branch,
+  double * out_best, double * out_second);
 int slam_ref_sensor(SlamRef * h, int m, const double * xy, int * out_assoc, double * out_dist, int * out_second_branch)
+{
+  return slam_ref_sensor_ex(h, m, xy, out_assoc, out_dist, out_second_branch, nullptr, nullptr);
+}
+// also: out_best[i] / out_second[i] = smallest / second-smallest distance of measurement i over the EXISTING
+// landmarks (the decision margins: a decision can only flip when out_best is within arithmetic noise of the
+// threshold or of out_second)
+int slam_ref_sensor_ex(
+  SlamRef * h, int m, const double * xy, int * out_assoc, double * out_dist, int * out_second_branch,
+  double * out_best, double * out_second)
 {
   int rc = 0;
   arma::reduce_log().clear();
@@ -177,6 +189,8 @@ int slam_ref_sensor(SlamRef * h, int m, const double * xy, int * out_assoc, doub
     if (log[p].kind != 'I' || log[p + 1].kind != 'M') {rc = rc ? rc : 2; h->error = "unexpected reduce log"; break;}
     int idx = static_cast<int>(log[p].index);
     const double mn = log[p + 1].value;
+    if (out_best) {out_best[meas] = log[p].head_best;}
+    if (out_second) {out_second[meas] = log[p].head_second;}
     p += 2;
     const bool again = p < log.size() && log[p].kind == 'I' && (p + 1 >= log.size() || log[p + 1].kind == 'I');
     if (again) {idx = static_cast<int>(log[p].index); ++p; ++second;}

@@ -49,6 +49,7 @@ def lib() -> C.CDLL:
         L.ekfo_predict.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double]
         L.ekfo_update_known.argtypes = [C.c_void_p, C.c_int, ip, dp, C.POINTER(C.c_ubyte)]
         L.ekfo_update_unknown.argtypes = [C.c_void_p, C.c_int, dp, ip]
+        L.ekfo_update_unknown_ex.argtypes = [C.c_void_p, C.c_int, dp, ip, dp, dp]
         L.ekfo_normalize_angle.restype = C.c_double
         L.ekfo_normalize_angle.argtypes = [C.c_double]
         _lib = L
@@ -144,3 +145,15 @@ class StructEkf:
         if rc:
             raise IndexError(f"oracle update_unknown failed rc={rc}")
         return assoc
+
+    def update_unknown_margins(self, xy):
+        """update_unknown that also returns (best, second) existing-landmark distance per measurement"""
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1)
+        m = len(xy) // 2
+        assoc = np.zeros(m, dtype=np.int32)
+        best, second = np.zeros(m), np.zeros(m)
+        rc = self._L.ekfo_update_unknown_ex(self._h, m, _dp(xy), assoc.ctypes.data_as(C.POINTER(C.c_int)),
+                                            _dp(best), _dp(second))
+        if rc:
+            raise IndexError(f"oracle update_unknown failed rc={rc}")
+        return assoc, best, second
