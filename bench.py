@@ -3,17 +3,33 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--landmarks N] [--m M]
 
-One "step" = one scan update of ONE filter: pose injection + prediction + m x (Mahalanobis
-association, gain, state update) + the fused covariance pass (BASELINE.json metric; config
-"single large map N=10,000 landmarks (n=20,003), 20 measurements/scan").  Prints ONE JSON line
-(contract in the task statement): `value` = scans/s with inputs resident in HBM, `e2e` = the same
-through the host-buffer C ABI call (H2D + D2H inside), `roofline` for the dominant kernel
-(ekf_downdate_kernel, HBM-bound), `cpu_baseline` = oracle B ("port") on the host cores.
+One "step" = one scan update of ONE filter: pose injection + prediction + m x (Mahalanobis association, gain,
+state update) + the fused covariance pass (BASELINE.json metric; configs[3] "single large map N=10,000
+landmarks (n=20,003), 20 measurements/scan").  Prints ONE JSON line (contract in the task statement):
 
-N > 1 GPUs: the SAME single map, Sigma row-sharded over the ranks (equal-area split, replicated
-sequential phase, one NCCL sum-all-reduce of the speculated column panel per scan):
-"strong" scaling.  The "batched" sub-object is BASELINE configs[2] (65,536 independent 20-landmark filters
-per GPU, one CTA each, no communication; weak scaling).
+  value         scans/s with inputs resident in HBM (ekf_scan_dev), CUDA events on the kernels' stream, no
+                per-scan events inside the timed region
+  e2e           the same through the host-buffer C-ABI call ekf_scan (H2D + D2H inside the timed region)
+  roofline      ekf_downdate_kernel (HBM-bound): algorithmic bytes / its mean launch time, taken live from a
+                second pass of K scans with per-scan events (ekf_enable_timing); `others` = the N = 60,000 pass
+                and the batched kernel
+  cpu_baseline  oracle B ("port": oracle/ekf_struct.c) on all host cores, WHOLE scans (every one of the m
+                measurements) continued from the GPU filter's own state, with the GPU/CPU parity of those very
+                scans (association identical, state, Sigma norm-wise and on the observed block) and the decision
+                margins; `others` = the batched configuration on a sample of filters, and the reference's own
+                compiled slam.cpp ("reference": oracle/_ref/libslam_ref.so) at its native N = 50
+  run           how this run was parallelised / what was checked (kept out of `config`, which is identical in
+                both arms)
+
+N > 1 GPUs: the SAME single map, Sigma row-sharded over the ranks (equal-area split, replicated sequential
+phase; per scan the owners store the speculated column panel straight into every rank's buffer over NVLink peer
+memory - `shard_push_cols_kernel` + arrival flags, no collective on the per-scan path):
+strong scaling, also at N = 1.  Sub-objects: `n60k` = BASELINE configs[4] (N = 60,000; one GPU holds the 57.7 GB
+triangle, N GPUs row-shard it), `batched` = configs[2] (65,536 independent 20-landmark filters PER GPU, one warp
+each, no communication: weak scaling).
+
+--impl reference: the reference's CPU algorithm on the host cores (oracle B; every measurement of every step), same
+config, metric and unit; rank 0 only.
 """
 from __future__ import annotations
 
@@ -34,6 +50,8 @@ for _p in (ROOT, os.path.join(ROOT, "oracle")):
 
 METRIC = "ekf_scan_updates_per_s_N10k"
 UNIT = "scan-updates/s"
+NOMINAL_HBM_GBS = 8000.0          # the "about 8 TB/s" of BASELINE.json's north star
+FP64_PEAK_TFLOPS = 37.1           # DMMA m8n8k4, measured on this pool: profiles/r1_fp64_peak_microbench.txt
 
 
 def parse_args():
@@ -47,6 +65,8 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=7)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the batched-filters section")
+    ap.add_argument("--no-n60k", action="store_true", help="skip the N = 60,000 section (BASELINE configs[4])")
+    ap.add_argument("--no-small", action="store_true", help="skip the N = 50 section (reference's native size)")
     ap.add_argument("--overlap", action="store_true",
                     help="single GPU: run the covariance pass of a scan behind the next scan's sequential side "
                          "(ekf_set_overlap; measured SLOWER at N=10k, DESIGN.md section 10 - kept for reproduction)")
@@ -54,8 +74,9 @@ def parse_args():
     ap.add_argument("--batch-landmarks", type=int, default=20)
     ap.add_argument("--batch-m", type=int, default=20)
     ap.add_argument("--batch-steps", type=int, default=10)
-    ap.add_argument("--cpu-sample-meas", type=int, default=2,
-                    help="measurements of one scan the CPU baseline actually runs (scaled to m)")
+    ap.add_argument("--n60k-steps", type=int, default=10)
+    ap.add_argument("--cpu-scans", type=int, default=6, help="whole scans the cpu_baseline leg runs at N=10k")
+    ap.add_argument("--cpu-batch-filters", type=int, default=2048, help="filters of the batched cpu_baseline sample")
     return ap.parse_args()
 
 
@@ -66,6 +87,15 @@ def peaks():
         with open(path) as fh:
             return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def config_of(N, m):
+    """the workload, identically worded in both arms"""
+    return {"workload": f"single large map N={N} landmarks (n={3 + 2 * N}), {m} measurements/scan, unknown "
+                        "association, all landmarks mapped (BASELINE.json configs[3])",
+            "landmarks": N, "m": m, "map": "ekf_fill_procedural(seed) / oracle/procedural_map.py: the same map in both arms",
+            "l2": f"inputs larger than L2: the covariance triangle ({8.0 * (3 + 2 * N) * (4 + 2 * N) / 2 / 1e9:.2f} GB) "
+                  "is streamed once per scan"}
 
 
 class ClockSampler:
@@ -118,9 +148,9 @@ class ClockSampler:
 
 
 def make_workload(state0, count, m, n_scans, seed):
-    """Per-scan poses and sightings for the large-map config: the robot circles in the middle of
-    the landmark grid; each scan sights the m nearest landmarks (body frame, sigma = 1e-3 per
-    axis like nusim's fake sensor, nusim.cpp:88,202,339-340)."""
+    """Per-scan poses and sightings for the large-map configs: the robot circles in the middle of the landmark
+    grid; each scan sights the m nearest landmarks (body frame, sigma = 1e-3 per axis like nusim's fake sensor,
+    nusim.cpp:88,202,339-340)."""
     rng = np.random.default_rng(seed)
     lm = state0[3:3 + 2 * count].reshape(-1, 2)
     side = np.sqrt(count)
@@ -149,82 +179,100 @@ def algorithmic_bytes(n, m):
     return 8.0 * n * (n + 1) + 8.0 * n * 9 * m, 8.0 * n * (n + 1)
 
 
-def cpu_setup(N, count, seed, state0=None, sigma_rows=None):
-    """Oracle B (oracle/ekf_struct.c) holding the large map: either a copy of the GPU filter's
-    state / Sigma, or a CPU-generated map of the same structure (block-diagonal SPD + rank-8)."""
+def oracle_threads():
     import struct_oracle as so
     L = so.lib()
     L.ekfo_num_threads.restype = int
-    cores = int(L.ekfo_num_threads())
+    return int(L.ekfo_num_threads())
+
+
+def cpu_filter_from_generator(N, seed):
+    """oracle B holding the SAME procedural map the GPU arm fills on the device (oracle/procedural_map.py is the
+    host re-implementation of ekf_fill_procedural)"""
+    import struct_oracle as so
+    from procedural_map import ProceduralMap
+    side = int(np.ceil(np.sqrt(N)))
+    pm = ProceduralMap(seed, N, N, side)
     o = so.StructEkf(n_landmarks=N)
-    n = o.n
-    if state0 is None:
-        rng = np.random.default_rng(seed)
-        side = int(np.ceil(np.sqrt(count)))
-        k = np.arange(count)
-        lm = np.stack([k % side + rng.uniform(-0.2, 0.2, count), k // side + rng.uniform(-0.2, 0.2, count)], 1)
-        o.state[3:3 + 2 * count] = lm.reshape(-1)
-        U = 0.01 * rng.uniform(-1, 1, (n, 8))
-        blk = 4096
-        for i0 in range(0, n, blk):
-            o.sigma[i0:i0 + blk, :] = U[i0:i0 + blk] @ U.T
-        idx = np.arange(n)
-        o.sigma[idx, idx] += 1e-3 * rng.uniform(1.0, 2.0, n)
-    else:
-        o.state[:] = state0
-        sigma_rows(o.sigma)
-    o.count = count
-    return o, cores
+    o.state[:] = pm.state()
+    for i0 in range(0, o.n, 2048):
+        i1 = min(o.n, i0 + 2048)
+        o.sigma[i0:i1, :] = pm.sigma0_rows(i0, i1)
+    o.count = N
+    return o
 
 
-def cpu_step(o, pose, xy_scan, m, sample_meas):
-    """One bounded sample of a scan: prediction + the first `sample_meas` measurements, the
-    measurement part scaled to m.  Returns the seconds a whole scan would take."""
-    t0 = time.perf_counter()
-    o.predict(*pose)
-    t1 = time.perf_counter()
-    o.update_unknown(xy_scan[:sample_meas])
-    t2 = time.perf_counter()
-    return (t1 - t0) + (t2 - t1) * m / sample_meas
-
-
-def cpu_desc(N, m, sample_meas, steps):
-    return (f"oracle B (oracle/ekf_struct.c: structured O(n^2)-per-measurement restatement of "
-            f"slam.cpp:321-489, pthreads on all host cores) at N={N}: per step, prediction + {sample_meas} of "
-            f"{m} measurements of a scan are run and the measurement part is scaled x{m}/{sample_meas}; {steps} step(s)")
-
-
+# ----------------------------------------------------------------------------------------------- reference arm
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm (oracle port; slam.cpp itself needs
-    Armadillo + ROS 2 and cannot be built here) on the host cores, same config and metric."""
+    """--impl reference: the reference's CPU algorithm on the host cores, same config, metric and unit.  slam.cpp
+    itself is compiled here (oracle/_ref/libslam_ref.so) but is O(n^3) per measurement and hard-wired dense: hours
+    per scan at N = 10,000, so the arm times oracle B, the structured restatement that the tests
+    pin to it; the `native_n50` entry times the reference's own object code at its native size."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     N, m = args.landmarks, args.m
-    o, cores = cpu_setup(N, N, args.seed)
+    o = cpu_filter_from_generator(N, args.seed)
+    cores = oracle_threads()
     total = args.warmup + args.steps
-    poses, xy, _ = make_workload(np.array(o.state), N, m, total, args.seed + 1)
+    poses, xy, ids = make_workload(np.array(o.state), N, m, total, args.seed + 100)
     o.set_prev(poses[0][1], poses[0][2])
-    secs = [cpu_step(o, poses[i], xy[i], m, args.cpu_sample_meas) for i in range(total)][args.warmup:]
+    secs, ok = [], True
+    for i in range(total):
+        t0 = time.perf_counter()
+        o.predict(*poses[i])
+        a = o.update_unknown(xy[i])
+        secs.append(time.perf_counter() - t0)
+        ok = ok and bool((np.asarray(a) == ids[i]).all())
     o.close()
+    secs = secs[args.warmup:]
     value = float(len(secs) / sum(secs))
-    desc = cpu_desc(N, m, args.cpu_sample_meas, args.steps)
+    desc = (f"oracle B (oracle/ekf_struct.c: structured O(n^2)-per-measurement restatement of slam.cpp:321-489, pthreads "
+            f"on all host cores) at N={N}: every step is one whole scan (prediction + all {m} measurements); "
+            f"{args.steps} step(s) after {args.warmup} warm-up")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / value, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"single large map N={N} landmarks (n={3 + 2 * N}), {m} measurements/scan, "
-                                   "unknown association, all landmarks mapped (BASELINE.json configs[3])",
-                       "landmarks": N, "m": m},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_of(N, m),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc,
+                             "association_equals_expected_ids": ok},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    if not args.no_small:
+        line["cpu_baseline"]["others"] = [native_n50_reference()]
     _emit(_OUT, json.dumps(line))
 
 
+def small_trace():
+    """BASELINE configs[1] stand-in at the reference's native size (N = 50, n = 103): circle drive, detections
+    only, shuffled, Mahalanobis association"""
+    from ekf_slam_b200 import synth
+    return [s for s in synth.circle_drive(n_scans=120, seed=1, drop_out_of_range=True, shuffle=True) if len(s.xy)]
+
+
+def native_n50_reference():
+    """the reference's own object code (slam.cpp compiled unmodified into oracle/_ref/libslam_ref.so) on its
+    native configuration, one host core"""
+    import slam_ref
+    if not slam_ref.available():
+        return {"config": "N=50", "unavailable": "oracle/_ref/libslam_ref.so not built (needs /root/reference)"}
+    scans = small_trace()
+    f = slam_ref.RefSlam(n_landmarks=50)
+    t0 = time.perf_counter()
+    for s in scans:
+        f.set_odometry(*s.odom)
+        f.sensor_cb([(x, y) for (x, y) in s.xy])
+    dt = time.perf_counter() - t0
+    return {"config": "N=50 (n=103), unknown association, circle drive around 4 landmarks (BASELINE configs[0]/[1] shape)",
+            "value": len(scans) / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": f"Slam::sensor_cb of the reference's slam.cpp compiled unmodified against the stub Armadillo "
+                      f"(oracle/stubs/armadillo: plain triple-loop products, no BLAS), {len(scans)} scans"}
+
+
+# ----------------------------------------------------------------------------------------------- batched filters
 def bench_batched(args, torch, ekf, stream, local, world, dist):
-    """BASELINE config 3: independent small filters, one CTA each, sharded over the ranks with no
-    communication (weak scaling: `--batch-filters` filters PER GPU).  Returns the sub-object that goes
-    into the JSON line under "batched"."""
+    """BASELINE config 3: independent small filters, one warp each, sharded over the ranks with no communication
+    (weak scaling: `--batch-filters` filters PER GPU)."""
     from ekf_slam_b200 import synth
     B, N, m = args.batch_filters, args.batch_landmarks, args.batch_m
     rank = int(os.environ.get("RANK", "0"))
@@ -273,6 +321,7 @@ def bench_batched(args, torch, ekf, stream, local, world, dist):
         exp = np.take_along_axis(pos, ids[s], axis=1)
         ok = ok and bool((d_assoc[s, :, :ids[s].shape[1]].cpu().numpy() == exp).all())
     ok = ok and g.last_status() == 0 and int(d_cnt.min()) == N
+
     # end to end: inputs in pinned host memory (as a producer would leave them), results into pinned host arrays
     def pin(a):
         t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
@@ -302,15 +351,287 @@ def bench_batched(args, torch, ekf, stream, local, world, dist):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(tt[0]), float(tt[1])
     byt = g.step_bytes(m)
-    g.close()
     peak, _ = peaks()
     value = world * B * K / (ms / 1000.0)
-    return {"metric": "ekf_batched_filter_steps_per_s", "value": value, "unit": "filter-steps/s",
-            "filters_per_gpu": B, "landmarks": N, "m": m, "steps": K, "ms_per_step": ms / K, "scaling": "weak",
-            "association_bit_exact_vs_expected_ids": ok, "gpu_launches": int(launches),
-            "bytes_per_filter_step": byt, "hbm_frac": (value / world * byt / 1e9) / peak,
-            "e2e": {"value": world * B * K / (e2e_ms / 1000.0), "unit": "filter-steps/s",
-                    "h2d_bytes_per_step": B * (24 + 16 * m), "d2h_bytes_per_step": B * (4 * m + 4 + 24) + 4}}
+    res = {"metric": "ekf_batched_filter_steps_per_s", "value": value, "unit": "filter-steps/s",
+           "filters_per_gpu": B, "landmarks": N, "m": m, "steps": K, "ms_per_step": ms / K, "scaling": "weak",
+           "association_bit_exact_vs_expected_ids": ok, "gpu_launches": int(launches),
+           "bytes_per_filter_step": byt, "hbm_frac": (value / world * byt / 1e9) / peak,
+           "e2e": {"value": world * B * K / (e2e_ms / 1000.0), "unit": "filter-steps/s",
+                   "h2d_bytes_per_step": B * (24 + 16 * m), "d2h_bytes_per_step": B * (4 * m + 4 + 24) + 4}}
+    if rank == 0 and not args.no_cpu_baseline:
+        res["cpu_baseline"] = batched_cpu_baseline(args, g, fields, h_pose, h_xy, ids, W, K)
+    g.close()
+    return res
+
+
+def batched_cpu_baseline(args, g, fields, h_pose, h_xy, ids, W, K):
+    """oracle B over a sample of the SAME filters (continued from the GPU filters' own state after the timed
+    steps), all host cores: one Python thread per core, each stepping its share of the sample (the C calls
+    release the GIL; a 43-dim filter never spawns the oracle's own worker threads)."""
+    import struct_oracle as so
+    from concurrent.futures import ThreadPoolExecutor
+    cores = os.cpu_count() or 1
+    Bs = min(args.cpu_batch_filters, args.batch_filters)
+    N, m = args.batch_landmarks, args.batch_m
+    S = 3                                     # steps per sampled filter
+    steps = list(range(W + K, W + K + S))
+    filt = []
+    for i in range(Bs):
+        o = so.StructEkf(n_landmarks=N)
+        o.state[:] = g.state(i); o.sigma[:] = g.sigma(i); o.count = g.count(i)
+        # filter_previous_configuration = the pose the filter ended its last scan with
+        o.set_prev(float(o.state[1]), float(o.state[2]))
+        filt.append(o)
+    ok = [True] * Bs
+
+    def work(lo, hi):
+        for i in range(lo, hi):
+            o = filt[i]
+            for s in steps:
+                o.predict(*h_pose[s][i])
+                a = o.update_unknown(h_xy[s][i])
+                ok[i] = ok[i] and len(a) == m
+    chunks = [(Bs * c // cores, Bs * (c + 1) // cores) for c in range(cores)]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(cores) as ex:
+        list(ex.map(lambda c: work(*c), chunks))
+    dt = time.perf_counter() - t0
+    for o in filt:
+        o.close()
+    return {"value": Bs * S / dt, "unit": "filter-steps/s", "cores": cores, "kind": "port",
+            "sample": f"oracle B on {Bs} of the {args.batch_filters} filters x {S} steps (N={N}, m={m}), continued from "
+                      f"the GPU filters' state, {cores} threads", "all_scans_completed": all(ok)}
+
+
+# ----------------------------------------------------------------------------------------------- one large map
+class MapRun:
+    """one large map on this process' GPU (or this rank's row shard of it)"""
+
+    def __init__(self, args, torch, dist, ekf, N, m, stream, local, world, rank):
+        self.torch, self.dist, self.world, self.rank = torch, dist, world, rank
+        self.N, self.m, self.n = N, m, 3 + 2 * N
+        self.sharded = world > 1
+        side = int(np.ceil(np.sqrt(N)))
+        if self.sharded:
+            from ekf_slam_b200 import shard
+            self.drv = shard.ShardedEkf(N, rank, world, local, stream=stream, max_scan=m)
+            self.f = self.drv.h
+            self.f.fill_procedural(args.seed, N, side)       # same seed everywhere: every rank fills its own rows
+            self.drv.sync()
+        else:
+            self.drv = None
+            self.f = ekf.EkfSlam(n_landmarks=N, device=local, max_scan=m)
+            self.f.set_stream(stream.cuda_stream)
+            self.f.fill_procedural(args.seed, N, side)
+        self.stream = stream
+        self.stored, self.n_pad = self.f.storage()
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def close(self):
+        (self.drv if self.sharded else self.f).close()
+
+    def run(self, args, K, W, local, overlap=False, clocks=True):
+        torch, dist, f, drv, m, N = self.torch, self.dist, self.f, self.drv, self.m, self.N
+        overlap = (not self.sharded) and overlap and f.set_overlap(True)
+        state0 = f.state()
+        n_scans = W + 3 * K                    # warm-up | timed | per-kernel timing | end to end
+        poses, xy, ids = make_workload(state0, N, m, n_scans, args.seed + 100)
+        f.set_previous_xy(poses[0][1], poses[0][2])
+        d_pose = torch.from_numpy(poses).cuda()
+        d_xy = torch.from_numpy(xy).cuda()
+        d_assoc = torch.full((n_scans, m), -9, dtype=torch.int32, device="cuda")
+        d_done = torch.full((n_scans,), m, dtype=torch.int32, device="cuda")
+
+        def scan_dev(s):
+            if self.sharded:
+                drv.scan_dev(d_pose[s], d_xy[s], d_assoc[s], check=False, done_t=d_done[s:s + 1])
+            else:
+                f.scan_dev(d_pose[s].data_ptr(), m, d_xy[s].data_ptr(), 0, 0, d_assoc[s].data_ptr())
+
+        # ---- device-resident throughput (`value`): no per-scan events in here -----------------------------
+        for s in range(W):
+            scan_dev(s)
+        l0 = f.launch_count()
+        sampler = ClockSampler(local)
+        if clocks:
+            sampler.start()
+            time.sleep(0.3)
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(self.stream)
+        for s in range(W, W + K):
+            scan_dev(s)
+        if overlap:
+            f.set_overlap(False)      # drain: `stream` waits for the last pass, so e1 closes over ALL the work
+        e1.record(self.stream)
+        self.barrier()
+        t1 = time.perf_counter()
+        clk = sampler.stop(t0, t1) if clocks else None
+        ms_total = e0.elapsed_time(e1)
+        launches = f.launch_count() - l0
+        status = f.last_status()
+        if overlap:
+            f.set_overlap(True)
+        # ---- per-kernel durations: the same K-scan loop again with the handle's per-scan events ------------
+        f.enable_timing(K)
+        for s in range(W + K, W + 2 * K):
+            scan_dev(s)
+        if overlap:
+            f.set_overlap(False)
+        self.barrier()
+        seq_ms, dd_ms = f.read_timing(K)
+        f.enable_timing(0)
+        if overlap:
+            f.set_overlap(True)
+        # ---- end to end through the host-buffer call (`e2e`) ----------------------------------------------
+        e_assoc = []
+        self.barrier()
+        t2 = time.perf_counter()
+        for s in range(W + 2 * K, W + 3 * K):
+            if self.sharded:
+                a, cnt, _, _ = drv.scan(poses[s], xy[s])
+            else:
+                a, cnt, _ = f.scan(poses[s], xy[s])
+            e_assoc.append(a)
+        self.barrier()
+        e2e_s = time.perf_counter() - t2
+
+        tt = torch.tensor([ms_total, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
+        if self.world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms = float(tt[0]), float(tt[1])
+        assoc_dev = d_assoc[W:W + 2 * K].cpu().numpy()
+        assoc_ok = bool((assoc_dev == ids[W:W + 2 * K]).all() and bool((d_done[:W + 2 * K] == m).all()) and
+                        all((np.asarray(a) == ids[W + 2 * K + i]).all() for i, a in enumerate(e_assoc)) and status == 0)
+        ok = torch.tensor([1 if assoc_ok else 0], device="cuda")
+        stored_all = torch.tensor([float(self.stored)], dtype=torch.float64, device="cuda")
+        if self.world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            dist.all_reduce(stored_all, op=dist.ReduceOp.SUM)
+        b_scan, b_pass = algorithmic_bytes(self.n, m)
+        peak, peak_src = peaks()
+        dd_avg_ms = float(np.mean(dd_ms)) if len(dd_ms) else float("nan")
+        # the covariance pass of this rank streams its share of the triangle: algorithmic bytes per launch
+        b_pass_rank = b_pass * self.stored / float(stored_all.item())
+        achieved = b_pass_rank / (dd_avg_ms * 1e-3) / 1e9
+        flops_rank = 2.0 * m * self.n * (self.n + 1) * self.stored / float(stored_all.item())
+        value = K / (ms_total / 1000.0)
+        self.poses, self.xy, self.ids, self.next_scan = poses, xy, ids, W + 3 * K
+        return {"value": value, "ms_per_step": ms_total / K, "e2e_value": K / (e2e_ms / 1000.0),
+                "e2e_ms_per_step": e2e_ms / K, "launches": int(launches), "assoc_ok": bool(ok.item()), "clocks": clk,
+                "overlap": bool(overlap),
+                "roofline": {"bound": "hbm", "kernel": "ekf_downdate_kernel", "achieved": achieved, "peak": peak,
+                             "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                             "frac_nominal_8tbs": achieved / NOMINAL_HBM_GBS,
+                             "algorithmic_bytes_per_launch": b_pass_rank, "avg_launch_ms": dd_avg_ms,
+                             "launch_time_source": f"handle CUDA events around every launch of a second pass of {K} scans "
+                                                   "(the timed region itself carries no per-scan events)",
+                             "fp64_tflops_achieved": flops_rank / (dd_avg_ms * 1e-3) / 1e12,
+                             "fp64_tflops_peak": FP64_PEAK_TFLOPS,
+                             "fp64_peak_source": "DMMA m8n8k4 microbenchmark on this pool (profiles/r1_fp64_peak_microbench.txt)",
+                             "seq_phase_avg_ms": float(np.mean(seq_ms)) if len(seq_ms) else None,
+                             "pass_share_of_step": dd_avg_ms / (ms_total / K),
+                             "scan_bytes": b_scan,
+                             "scan_frac_of_hbm_roofline": (b_scan * value / 1e9) / (peak * self.world),
+                             "scan_frac_of_nominal_8tbs": (b_scan * value / 1e9) / (NOMINAL_HBM_GBS * self.world)}}
+
+
+def parity_and_cpu_baseline(args, run):
+    """The cpu_baseline leg at N = 10,000: oracle B continues from the GPU filter's own state and runs WHOLE scans;
+    the GPU runs the same scans.  Returns the baseline object, with the parity of those scans and the decision
+    margins oracle B saw."""
+    import struct_oracle as so
+    f, N, m, n = run.f, run.N, run.m, run.n
+    S = max(1, args.cpu_scans)
+    o = so.StructEkf(n_landmarks=N)
+    o.state[:] = f.state()
+    for i0 in range(0, n, 2048):
+        i1 = min(n, i0 + 2048)
+        o.sigma[i0:i1, :] = f.sigma_block(i0, i1, 0, n)
+    o.count = N
+    o.set_prev(*f.previous_xy())
+    s0 = run.next_scan - S                    # re-uses the tail of the workload (the filter is in steady state)
+    secs, same, best, second, touched = [], True, [], [], set()
+    thr = 2.0
+    for s in range(s0, s0 + S):
+        t0 = time.perf_counter()
+        o.predict(*run.poses[s])
+        a, b1, b2 = o.update_unknown_margins(run.xy[s])
+        secs.append(time.perf_counter() - t0)
+        ag, _, _ = f.scan(run.poses[s], run.xy[s])
+        same = same and list(ag) == list(a)
+        best += list(b1); second += list(b2)
+        touched.update(int(k) for k in a)
+    best, second = np.array(best), np.array(second)
+    # parity of the two filters after those scans: state, Sigma norm-wise over sampled full-width block rows, and
+    # the observed block (pose + every landmark sighted in these scans)
+    st = f.state()
+    state_rel = float(np.linalg.norm(st - o.state) / np.linalg.norm(o.state))
+    worst = 0.0
+    for i0 in list(np.linspace(0, n - 256, 12).astype(int)):
+        dev = f.sigma_block(int(i0), int(i0) + 256, 0, n)
+        ref = o.sigma[int(i0):int(i0) + 256, :]
+        worst = max(worst, float(np.linalg.norm(dev - ref) / np.linalg.norm(ref)))
+    idx = [0, 1, 2] + [3 + 2 * k + e for k in sorted(touched) for e in (0, 1)]
+    dev = np.stack([f.sigma_block(i, i + 1, 0, n)[0, idx] for i in idx])
+    ref = np.array(o.sigma)[np.ix_(idx, idx)] if n <= 4096 else np.stack([np.asarray(o.sigma[i, :])[idx] for i in idx])
+    active_rel = float(np.linalg.norm(dev - ref) / np.linalg.norm(ref))
+    o.close()
+    value = S / sum(secs)
+    return {"value": value, "unit": UNIT, "cores": oracle_threads(), "kind": "port",
+            "sample": f"oracle B (oracle/ekf_struct.c, pthreads on all host cores) at N={N}: {S} WHOLE scans (prediction + "
+                      f"all {m} measurements each), continued from the GPU filter's own state and Sigma",
+            "parity_of_these_scans": {"association_identical": bool(same), "state_rel": state_rel,
+                                      "sigma_rel_normwise_worst_block_row": worst,
+                                      "sigma_rel_observed_block": active_rel,
+                                      "observed_block_dim": len(idx)},
+            "decision_margins": {"source": "oracle B, every measurement of these scans",
+                                 "min_rel_gap_best_to_threshold": float(np.min(np.abs(best - thr) / thr)),
+                                 "min_rel_gap_best_to_second": float(np.min((second - best) / np.maximum(best, 1e-300))),
+                                 "measurements": int(len(best))}}
+
+
+def small_gpu_vs_reference(ekf, local):
+    """N = 50 (the reference's native size): the same trace through ekf_scan and through the reference's compiled
+    slam.cpp - throughput of both and the parity of the final filters"""
+    import slam_ref
+    from ekf_slam_b200 import synth
+    ref = native_n50_reference()
+    if "unavailable" in ref:
+        return ref
+    scans = small_trace()
+    r = slam_ref.RefSlam(n_landmarks=50)
+    g = ekf.EkfSlam(n_landmarks=50, device=local)
+    host = synth.MapHost()
+    same = True
+    t_gpu = 0.0
+    for s in scans:
+        r.set_odometry(*s.odom)
+        ar = r.sensor_cb([(x, y) for (x, y) in s.xy])
+        x, y, th = host.composed(s.odom)
+        t0 = time.perf_counter()
+        ag, _, pose = g.scan((th, x, y), s.xy)
+        t_gpu += time.perf_counter() - t0
+        host.after_update(tuple(pose), s.odom)
+        same = same and list(ag) == list(ar)
+    sg, sr = g.state(), r.state
+    SG, SR = g.sigma(), r.sigma
+    k = 3 + 2 * r.counter_obstacles
+    ref["gpu"] = {"value": len(scans) / t_gpu, "unit": UNIT, "path": "ekf_scan, host buffers, one scan per call (latency-bound)"}
+    ref["parity_vs_reference_object_code"] = {
+        "association_identical": bool(same),
+        "state_rel": float(np.linalg.norm(sg - sr) / np.linalg.norm(sr)),
+        "sigma_rel_normwise": float(np.linalg.norm(SG - SR) / np.linalg.norm(SR)),
+        "sigma_rel_observed_block": float(np.linalg.norm(SG[:k, :k] - SR[:k, :k]) / np.linalg.norm(SR[:k, :k]))}
+    g.close()
+    return ref
 
 
 def run_ours(args):
@@ -327,171 +648,110 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N, m, K, W = args.landmarks, args.m, args.steps, args.warmup
-    n = 3 + 2 * N
-    side = int(np.ceil(np.sqrt(N)))
     # a non-default stream: the legacy default stream's handle is NULL, which ekf_set_stream reads as
     # "use the handle's own stream" - the timing events must sit on the stream the kernels use
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
-    sharded = world > 1
-    if sharded:
-        # ONE map row-sharded over the ranks (BASELINE configs[3] "row-sharded Sigma"): strong scaling
-        from ekf_slam_b200 import shard
-        drv = shard.ShardedEkf(N, rank, world, local, stream=stream, max_scan=m)
-        f = drv.h
-        f.fill_procedural(args.seed, N, side)       # same seed everywhere: every rank fills its own rows
-        drv.sync()
-    else:
-        f = ekf.EkfSlam(n_landmarks=N, device=local, max_scan=m)
-        f.set_stream(stream.cuda_stream)
-        f.fill_procedural(args.seed, N, side)
-    # --overlap: the covariance pass of scan s runs (out of place, second stream) behind the sequential side of
-    # scan s+1 - ekf_set_overlap; needs a second covariance buffer, stays off when that does not fit
-    overlap = (not sharded) and args.overlap and f.set_overlap(True)
-    state0 = f.state()
-    n_scans = 2 * (W + K)
-    poses, xy, ids = make_workload(state0, N, m, n_scans, args.seed + 100)
-    f.set_previous_xy(poses[0][1], poses[0][2])
-    d_pose = torch.from_numpy(poses).cuda()
-    d_xy = torch.from_numpy(xy).cuda()
-    d_assoc = torch.full((n_scans, m), -9, dtype=torch.int32, device="cuda")
-    d_done = torch.full((n_scans,), m, dtype=torch.int32, device="cuda")
-    stored, n_pad = f.storage()
 
-    def scan_dev(s):
-        if sharded:
-            drv.scan_dev(d_pose[s], d_xy[s], d_assoc[s], check=False, done_t=d_done[s:s + 1])
+    run = MapRun(args, torch, dist, ekf, N, m, stream, local, world, rank)
+    res = run.run(args, K, W, local, overlap=args.overlap)
+    roof = res["roofline"]
+    prof = os.path.join(ROOT, "profiles", "downdate_traffic.json")
+    if os.path.exists(prof) and world == 1 and N == 10000 and m == 20:
+        with open(prof) as fh:
+            tj = json.load(fh)
+        roof["traffic"] = tj.get("dram_bytes_per_launch")
+        roof["traffic_source"] = ("committed ncu --set full capture of this kernel at this size ("
+                                  + str(tj.get("source", "profiles/")) + "), not measured in this run")
+    cpu = None
+    if not args.no_cpu_baseline and world == 1 and rank == 0:
+        cpu = parity_and_cpu_baseline(args, run)
+    stored_gb = 8.0 * run.n * (run.n + 1) / 2 / 1e9
+    n_pad = run.n_pad
+    run.close()
+    del run
+    torch.cuda.empty_cache()
+
+    n60k = None
+    if not args.no_n60k:
+        free, _ = torch.cuda.mem_get_info()
+        need = 8.0 * 120003 * 120004 / 2 / world * 1.08 + 2e9
+        if free < need:
+            n60k = {"unavailable": f"needs {need / 1e9:.0f} GB of free HBM per GPU, {free / 1e9:.0f} GB free"}
         else:
-            f.scan_dev(d_pose[s].data_ptr(), m, d_xy[s].data_ptr(), 0, 0, d_assoc[s].data_ptr())
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- device-resident throughput (`value`) -------------------------------------------------
-    for s in range(W):
-        scan_dev(s)
-    f.enable_timing(K)
-    l0 = f.launch_count()
-    sampler = ClockSampler(local)
-    sampler.start()
-    time.sleep(0.3)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0 = time.perf_counter()
-    e0.record(stream)
-    for s in range(W, W + K):
-        scan_dev(s)
-    if overlap:
-        f.set_overlap(False)      # drain: `stream` waits for the last pass, so e1 closes over ALL the work
-    e1.record(stream)
-    barrier()
-    t1 = time.perf_counter()
-    clocks = sampler.stop(t0, t1)
-    ms_total = e0.elapsed_time(e1)
-    launches = f.launch_count() - l0
-    seq_ms, dd_ms = f.read_timing(K)
-    f.enable_timing(0)
-    status = f.last_status()
-    if overlap:
-        f.set_overlap(True)
-
-    # ---- end to end through the host-buffer call (`e2e`) ---------------------------------------
-    e_assoc = []
-    barrier()
-    t2 = time.perf_counter()
-    for s in range(W + K, W + 2 * K):
-        if sharded:
-            a, cnt, _, _ = drv.scan(poses[s], xy[s])
-        else:
-            a, cnt, _ = f.scan(poses[s], xy[s])
-        e_assoc.append(a)
-    barrier()
-    t3 = time.perf_counter()
-    e2e_s = t3 - t2
-
-    tt = torch.tensor([ms_total, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms = float(tt[0]), float(tt[1])
-    assoc_dev = d_assoc[W:W + K].cpu().numpy()
-    assoc_ok = bool((assoc_dev == ids[W:W + K]).all() and bool((d_done[:W + K] == m).all()) and
-                    all((np.asarray(a) == ids[W + K + i]).all() for i, a in enumerate(e_assoc)) and status == 0)
-    ok = torch.tensor([1 if assoc_ok else 0], device="cuda")
-    if world > 1:
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    stored_all = torch.tensor([float(stored)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(stored_all, op=dist.ReduceOp.SUM)
+            K6 = args.n60k_steps
+            r6 = MapRun(args, torch, dist, ekf, 60000, m, stream, local, world, rank)
+            x6 = r6.run(args, K6, 2, local, clocks=False)
+            r6.close()
+            del r6
+            torch.cuda.empty_cache()
+            n60k = {"metric": "ekf_scan_updates_per_s_N60k", "value": x6["value"], "unit": UNIT, "n_gpus": world,
+                    "steps": K6, "warmup": 2, "ms_per_step": x6["ms_per_step"], "scaling": "strong",
+                    "config": "single huge map N=60,000 landmarks (n=120,003; 57.7 GB stored triangle), 20 "
+                              "measurements/scan (BASELINE.json configs[4])" + (f", row-sharded over {world} GPUs" if world > 1 else ""),
+                    "association_bit_exact_vs_expected_ids": x6["assoc_ok"],
+                    "e2e": {"value": x6["e2e_value"], "unit": UNIT, "ms_per_step": x6["e2e_ms_per_step"]},
+                    "gpu_launches": x6["launches"], "roofline": x6["roofline"]}
 
     batched = None
     if not args.no_batched:
         batched = bench_batched(args, torch, ekf, stream, local, world, dist)
+    small = None
+    if not args.no_small and rank == 0 and not args.no_cpu_baseline:
+        small = small_gpu_vs_reference(ekf, local)
 
     if rank != 0:
-        (drv if sharded else f).close()
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # one scan update of ONE map per step: with several GPUs the same map is row-sharded (strong scaling)
-    value = K / (ms_total / 1000.0)
-    e2e_value = K / (e2e_ms / 1000.0)
-    b_scan, b_pass = algorithmic_bytes(n, m)
-    peak, peak_src = peaks()
-    dd_avg_ms = float(np.mean(dd_ms)) if len(dd_ms) else float("nan")
-    # the covariance pass of this rank streams its share of the triangle: algorithmic bytes per launch
-    b_pass_rank = b_pass * stored / float(stored_all.item())
-    achieved = b_pass_rank / (dd_avg_ms * 1e-3) / 1e9
-    traffic = None
-    prof = os.path.join(ROOT, "profiles", "downdate_traffic.json")
-    if os.path.exists(prof) and world == 1 and N == 10000 and m == 20:
-        with open(prof) as fh:
-            traffic = json.load(fh).get("dram_bytes_per_launch")
+    others = []
+    if n60k is not None and "roofline" in n60k:
+        r6 = n60k["roofline"]
+        others.append({"kernel": "ekf_downdate_kernel", "config": "N=60000 (BASELINE configs[4])", "bound": "hbm",
+                       "achieved": r6["achieved"], "peak": r6["peak"], "unit": "GB/s", "frac": r6["frac"],
+                       "avg_launch_ms": r6["avg_launch_ms"], "seq_phase_avg_ms": r6["seq_phase_avg_ms"],
+                       "scan_updates_per_s": n60k["value"], "e2e_scan_updates_per_s": n60k["e2e"]["value"]})
+    if batched is not None:
+        others.append({"kernel": "ekf_batch_kernel", "config": f"{batched['filters_per_gpu']} filters/GPU x N={batched['landmarks']}, "
+                                                               f"m={batched['m']} (BASELINE configs[2])",
+                       "bound": "fp64 issue / latency (not HBM: see DESIGN.md section 6)", "unit": "GB/s",
+                       "achieved": batched["hbm_frac"] * roof["peak"], "peak": roof["peak"], "frac": batched["hbm_frac"],
+                       "filter_steps_per_s": batched["value"], "e2e_filter_steps_per_s": batched["e2e"]["value"]})
+    roof["others"] = others
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong" if sharded else "weak",
+        "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"single large map N={N} landmarks (n={n}), {m} measurements/scan, unknown "
-                               "association, all landmarks mapped (BASELINE.json configs[3])",
-                   "landmarks": N, "m": m,
-                   "parallelism": (f"one map, Sigma row-sharded over {world} GPUs (equal-area), one NCCL sum-all-reduce "
-                                   f"of the {m}x{n_pad}x2 column panel per scan") if sharded else "1 GPU",
-                   "l2": f"inputs larger than L2: Sigma triangle = {float(stored_all.item()) * 8 / 1e9:.2f} GB streamed "
-                         "per scan",
-                   "overlap": ("covariance pass of scan s runs out of place on a second stream behind the sequential "
-                               "side of scan s+1 (ekf_set_overlap); the timed region ends after the last pass")
-                              if overlap else "off (pass and sequential phase back to back on one stream)",
-                   "association_bit_exact_vs_expected_ids": bool(ok.item())},
-        "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 24 + 16 * m, "d2h_bytes_per_step": 32 + 4 * m,
-                "ms_per_step": e2e_ms / K},
-        "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "ekf_downdate_kernel", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": b_pass_rank, "avg_launch_ms": dd_avg_ms,
-                     "seq_phase_avg_ms": float(np.mean(seq_ms)) if len(seq_ms) else None,
-                     "scan_frac_of_hbm_roofline": (b_scan * value / 1e9) / (peak * world)},
+        "config": config_of(N, m),
+        "run": {"parallelism": (f"one map, Sigma row-sharded over {world} GPUs (equal-area split); per scan the owners "
+                                f"store the {m}x{n_pad}x2 speculated column panel into every rank's buffer over NVLink peer "
+                                "memory (shard_push_cols_kernel + arrival flags), no collective on the per-scan path")
+                               if world > 1 else "1 GPU",
+                "overlap": ("covariance pass of scan s runs out of place on a second stream behind the sequential "
+                            "side of scan s+1 (ekf_set_overlap); the timed region ends after the last pass")
+                           if res["overlap"] else "off (pass and sequential phase back to back on one stream)",
+                "association_bit_exact_vs_expected_ids": res["assoc_ok"],
+                "stored_triangle_gb": stored_gb},
+        "clocks": res["clocks"],
+        "e2e": {"value": res["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 24 + 16 * m, "d2h_bytes_per_step": 32 + 4 * m,
+                "ms_per_step": res["e2e_ms_per_step"]},
+        "gpu_launches": res["launches"],
+        "roofline": roof,
     }
+    if n60k is not None:
+        line["n60k"] = n60k
     if batched is not None:
         line["batched"] = batched
-    if not args.no_cpu_baseline and world == 1:
-        def fill_rows(sig):
-            rows = 2048
-            for i0 in range(0, n, rows):
-                i1 = min(n, i0 + rows)
-                sig[i0:i1, :] = f.sigma_block(i0, i1, 0, n)
-        o, cores = cpu_setup(N, N, args.seed, state0=f.state(), sigma_rows=fill_rows)
-        s0 = W + 2 * K - 1
-        o.set_prev(*f.previous_xy())
-        secs = cpu_step(o, poses[s0], xy[s0], m, args.cpu_sample_meas)
-        o.close()
-        line["cpu_baseline"] = {"value": 1.0 / secs, "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": cpu_desc(N, m, args.cpu_sample_meas, 1)}
-    (drv if sharded else f).close()
+    if cpu is not None:
+        oth = []
+        if batched is not None and "cpu_baseline" in batched:
+            oth.append(dict(batched["cpu_baseline"], config="batched (BASELINE configs[2])"))
+        if small is not None:
+            oth.append(small)
+        cpu["others"] = oth
+        line["cpu_baseline"] = cpu
     if world > 1:
         dist.destroy_process_group()
     _emit(_OUT, json.dumps(line))

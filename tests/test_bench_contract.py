@@ -28,6 +28,23 @@ def test_reference_arm_line():
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["gpu_launches"] == 0
+    # every step is a WHOLE scan (all m measurements): `steps` means steps, nothing is projected
+    assert "whole scan" in cb["sample"] and cb["association_equals_expected_ids"] is True
+    assert d["scaling"] == "strong"
+    # the reference's own compiled slam.cpp is timed at its native size beside it
+    native = cb["others"][0]
+    assert native["kind"] == "reference" and native["value"] > 0 and native["cores"] == 1
+
+
+def test_both_arms_describe_the_workload_identically():
+    """the driver compares the two arms' `config` objects: both come from the one function"""
+    sys.path.insert(0, ROOT)
+    import importlib
+    bench = importlib.import_module("bench")
+    src = open(os.path.join(ROOT, "bench.py")).read()
+    assert src.count('"config": config_of(N, m)') == 2
+    c = bench.config_of(10000, 20)
+    assert set(c) == {"workload", "landmarks", "m", "map", "l2"} and "model" not in c
 
 
 def test_reference_arm_under_torchrun_only_rank0_prints():
