@@ -103,6 +103,7 @@ struct ekf_filter {
   cudaEvent_t ev_seq[2] = {nullptr, nullptr}, ev_pass[2] = {nullptr, nullptr};
   int64_t pipe_step = 0;         // rounds issued since the pipeline was entered
   int pipe_k2_prev = 0;          // panel columns of the previous round's pass
+  int slot_cap = 1;              // CTAs the arg-min slot arrays hold (<= 32 * kMaxSlotsPerLane)
   int pipe_grid = 1;             // CTAs of the sequential kernel that fit beside the pass (<= one per SM)
   int *done_host = nullptr;      // pinned: measurements the last round processed
   cudaEvent_t done_event = nullptr;

@@ -182,6 +182,7 @@ int ekf_create(const ekf_config *cfg, ekf_filter **out) {
   f->dd_ctas = env_int("EKF_DD_CTAS", 2);
   if (f->dd_ctas < 1) f->dd_ctas = 1;
   if (f->dd_prefetch < 0) f->dd_prefetch = 0;
+  f->slot_cap = seq_cap;
   CKC(cudaMalloc(&f->slot_d, (size_t)kSlotReps * 2 * seq_cap * sizeof(double)));
   CKC(cudaMalloc(&f->slot_k, (size_t)kSlotReps * 2 * seq_cap * sizeof(int)));
   CKC(cudaMalloc(&f->slot_rec, (size_t)kSlotReps * 2 * seq_cap * kRecStride * sizeof(double)));

@@ -98,7 +98,16 @@ int pipe_resources_alloc(ekf_filter *f) {
                              cudaSharedmemCarveoutMaxShared));
   int blocks = (f->N + kSeqThreadsSmall - 1) / kSeqThreadsSmall;
   f->pipe_grid = blocks < f->num_sms ? blocks : f->num_sms;   // one 64-thread CTA per SM beside the pass
+  // the arg-min slot arrays (and the one-warp slot scan) are sized for the classic grid: never launch more CTAs
+  // than they hold, whatever the SM count of the device
+  if (f->pipe_grid > f->slot_cap) f->pipe_grid = f->slot_cap;
   if (f->pipe_grid < 1) f->pipe_grid = 1;
+  // residency check for the plain launch: the kernel alone must fit pipe_grid CTAs (one per SM at least); the bounded
+  // barrier covers what this cannot see (the pass and other clients of the device)
+  int occ = 0;
+  CK(f, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ekf_seq_kernel<kSeqThreadsSmall>, kSeqThreadsSmall,
+                                                      seq_smem_bytes(kSeqThreadsSmall)));
+  if (occ < 1) return EKF_ERR_INVALID;
   return shard_buffers(f);
 }
 

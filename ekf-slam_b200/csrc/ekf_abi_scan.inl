@@ -127,12 +127,17 @@ int overlap_round(ekf_filter *f, const double *pose_dev, int mc, const double *x
   sp.bar = f->bar; sp.bar_base = f->bar_base;
   sp.slot_d = f->slot_d; sp.slot_k = f->slot_k; sp.slot_rec = f->slot_rec;
   f->bar_base += (unsigned long long)mc * (unsigned long long)f->pipe_grid;
+  // plain launch below: the hand-written grid barrier then has no residency guarantee from the driver (another
+  // handle's kernels, another process or a long-running kernel may hold SMs), so its wait is bounded - a grid that
+  // is only partly resident latches EKF_ERR_CUDA after this long instead of hanging the GPU
+  sp.bar_timeout_ns = (unsigned long long)env_int("EKF_PIPE_BARRIER_TIMEOUT_MS", 2000) * 1000000ULL;
   // NOT a cooperative launch: the driver holds a cooperative grid back until the device is otherwise idle, which
   // would put it behind the very pass it is meant to overlap.  Co-residency - all the hand-written grid barrier
   // needs - holds by construction: at most one CTA per SM, and a CTA fits beside the pass's CTA (registers, shared
   // memory); the only other kernels that can be resident (the pass on the back stream, other handles' kernels) never
   // wait for this one.
   if (env_int("EKF_PIPE_COOP", 0)) {
+    sp.bar_timeout_ns = 0;
     void *args[] = {(void *)&sp};
     CK(f, cudaLaunchCooperativeKernel((const void *)ekf_seq_kernel<kSeqThreadsSmall>, dim3(f->pipe_grid),
                                       dim3(kSeqThreadsSmall), args, seq_smem_bytes(kSeqThreadsSmall), f->stream));
@@ -194,7 +199,16 @@ int scan_overlap(ekf_filter *f, const double *pose_dev, int m, const double *xy_
                                  assoc_dev ? assoc_dev + t0 : nullptr, t0 + mc >= m, pose_out_dev, cnt_out_dev, res_bytes,
                                  &done);
     if (rc != EKF_OK) return rc;
-    if (done < 0 || done > mc) return EKF_ERR_CUDA;
+    if (done < 0 || done > mc) {
+      // the bounded grid barrier gave up (done == -1) or the device wrote nonsense: wait for every CTA of the launch
+      // to leave, then start the arrival counter afresh so that the handle stays usable on the classic path
+      cudaStreamSynchronize(f->stream);
+      if (f->back_stream) cudaStreamSynchronize(f->back_stream);
+      cudaMemsetAsync(f->bar, 0, sizeof(unsigned long long), f->stream);
+      f->bar_base = 0;
+      f->cuda_err = "overlapped sequential kernel: grid barrier timed out (grid not co-resident)";
+      return EKF_ERR_CUDA;
+    }
     first = false;
     t0 += done;
     if (done == 0) break;       // a round that cannot get past its first sighting: finish the scan classically

@@ -61,6 +61,7 @@ constexpr size_t seq_smem_bytes(int nt, bool hot = false) {
 // status codes latched on the device (values of ekf_status in include/ekf_slam_b200.h)
 constexpr int kErrCapacity = 2;
 constexpr int kErrBadId = 4;
+constexpr int kErrCuda = 5;
 
 struct SeqParams {
   // geometry / constants
@@ -99,6 +100,7 @@ struct SeqParams {
   // grid barrier + arg-min slots
   unsigned long long *bar;
   unsigned long long bar_base;
+  unsigned long long bar_timeout_ns;   // 0: cooperative launch, wait for ever; > 0: plain launch, bounded wait
   // every CTA publishes its best candidate kSlotReps times; CTA b reads replica b % kSlotReps.  A single
   // copy made ~300 warps read the same few L2 lines right after the barrier, and the L2 slice serving
   // a line handles those requests one after the other (3.6 us per measurement, tools/seq_phase_probe.py)
@@ -124,18 +126,56 @@ constexpr int kMaxSlotsPerLane = 5;       // gridDim <= 32 * kMaxSlotsPerLane (o
 constexpr int kRecDoubles = 22;
 constexpr int kRecStride = 24;
 
+// One arrival counter for the whole grid.  Arrival = release add (orders the CTA's earlier stores - its slot, its
+// hot-winner push - before the count; the CTA's own threads are ordered before it by the bar.sync above), wait =
+// acquire loads.  SASS: MEMBAR.ALL.GPU + REDG (no return value) / LDG.STRONG.GPU + CCTL.IVALL per poll.  The first
+// version bracketed an ATOMG with two __threadfence() (MEMBAR.SC.GPU each, the second one on the critical path
+// right after the last arrival): -DEKF_SEQ_FENCE_BARRIER keeps it for A/B runs (tools/seq_soak.py).
 __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long target) {
   __syncthreads();
   if (threadIdx.x == 0) {
+    unsigned long long v;
+#ifdef EKF_SEQ_FENCE_BARRIER
     __threadfence();
     atomicAdd(bar, 1ULL);
-    unsigned long long v;
     do {
       asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
     } while (v < target);
     __threadfence();
+#else
+    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(bar), "l"(1ULL) : "memory");
+    do {
+      asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+    } while (v < target);
+#endif
   }
   __syncthreads();
+}
+
+// The same barrier for launches that are NOT cooperative (the overlapped path starts the kernel plainly so that it
+// may run beside the covariance pass): nothing guarantees that every CTA is resident, so the wait is bounded.
+// Returns true (to every thread of the CTA) when the count did not arrive within timeout_ns; the caller latches
+// EKF_ERR_CUDA and leaves the kernel instead of hanging the device.
+__device__ __forceinline__ bool grid_barrier_bounded(unsigned long long *bar, unsigned long long target,
+                                                     unsigned long long timeout_ns) {
+  __syncthreads();
+  int late = 0;
+  if (threadIdx.x == 0) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(bar), "l"(1ULL) : "memory");
+    unsigned long long v, t0 = 0;
+    unsigned polls = 0;
+    for (;;) {
+      asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+      if (v >= target) break;
+      if ((++polls & 1023u) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > timeout_ns) { late = 1; break; }
+      }
+    }
+  }
+  return __syncthreads_or(late) != 0;
 }
 
 __device__ __forceinline__ double ldcg_d(const double *p) { return __ldcg(p); }
@@ -392,7 +432,16 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
 
     // ---- B: the one grid barrier of this measurement ----------------------------------------
     SEQ_STAMP(2);
-    grid_barrier(p.bar, p.bar_base + (unsigned long long)(t + 1) * gridDim.x);
+    if (p.bar_timeout_ns == 0) {
+      grid_barrier(p.bar, p.bar_base + (unsigned long long)(t + 1) * gridDim.x);
+    } else if (grid_barrier_bounded(p.bar, p.bar_base + (unsigned long long)(t + 1) * gridDim.x, p.bar_timeout_ns)) {
+      // part of the grid never became resident: report instead of spinning (the host resets the counter)
+      if (tid == 0) {
+        atomicMax(p.status, kErrCuda);
+        if (p.done_out) atomicExch(p.done_out, -1);
+      }
+      return;
+    }
     SEQ_STAMP(3);
 
     // ---- C: decision + the winner's record: warps 0 and 1 only (two requesters per CTA on the slot
@@ -776,7 +825,17 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
   // ---------------- epilogue: slam.cpp:273-274,291 / :490-491,508 ---------------------------------
   // a scan without measurements has passed no grid barrier yet: the global pose block / pose state
   // below may only be rewritten once every CTA has read the old ones
-  if (p.m == 0) grid_barrier(p.bar, p.bar_base + gridDim.x);
+  if (p.m == 0) {
+    if (p.bar_timeout_ns == 0) {
+      grid_barrier(p.bar, p.bar_base + gridDim.x);
+    } else if (grid_barrier_bounded(p.bar, p.bar_base + gridDim.x, p.bar_timeout_ns)) {
+      if (tid == 0) {
+        atomicMax(p.status, kErrCuda);
+        if (p.done_out) atomicExch(p.done_out, -1);
+      }
+      return;
+    }
+  }
   if (blockIdx.x == 0 && tid == 0) {
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
