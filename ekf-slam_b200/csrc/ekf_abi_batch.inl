@@ -15,6 +15,11 @@ struct ekf_batch {
   unsigned char *io_dev = nullptr, *io_host = nullptr, *res_dev = nullptr, *res_host = nullptr;
   size_t io_cap = 0, res_cap = 0;
   cudaStream_t own_stream = nullptr, stream = nullptr;
+  // host-buffer steps on page-locked caller memory are split into chunks of filters that alternate between two
+  // side streams, so that the H2D copy of chunk c+1, the kernel of chunk c and the D2H copy of chunk c-1 overlap
+  cudaStream_t side[2] = {nullptr, nullptr};
+  cudaEvent_t ev_begin = nullptr, ev_side[2] = {nullptr, nullptr};
+  int chunks = 1;
   int64_t launches = 0;
   int latched = EKF_OK;
 };
@@ -34,9 +39,12 @@ constexpr int BATCH_DEFAULT_VARIANT = 6;   // one-pass association + DMMA 8x8-ti
   } while (0)
 
 int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, const int32_t *ids,
-                 const int32_t *m_count, int32_t *assoc, int32_t *count, double *pose_out) {
+                 const int32_t *m_count, int32_t *assoc, int32_t *count, double *pose_out, int f0 = 0, int nf = -1,
+                 cudaStream_t stream = nullptr) {
+  if (nf < 0) nf = b->B - f0;
+  if (!stream) stream = b->stream;
   BatchParams p{};
-  p.B = b->B; p.N = b->N; p.n = b->n; p.tri = b->tri;
+  p.B = b->B; p.N = b->N; p.n = b->n; p.tri = b->tri; p.f0 = f0;
   p.q_noise = b->cfg.q_noise; p.r_noise = b->cfg.r_noise; p.thr = b->cfg.mah_threshold;
   p.sigma = b->sigma; p.mu = b->mu; p.prev = b->prev; p.cnt = b->cnt; p.status = b->status;
   p.tri_map = b->tri_map; p.blk_map = b->blk_map; p.nblk = b->nblk; p.soff = b->soff;
@@ -45,7 +53,7 @@ int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, con
   const size_t smem = batch_smem_bytes(b->n, m, b->variant & 3);
   if (smem > 200 * 1024) return EKF_ERR_INVALID;   // m beyond the per-CTA shared memory
 #define EKF_BATCH_CASE(V, MINB, ONE, DD) \
-  case V: ekf_batch_kernel<MINB, ONE, DD><<<b->B, kBatchThreads, smem, b->stream>>>(p); break;
+  case V: ekf_batch_kernel<MINB, ONE, DD><<<nf, kBatchThreads, smem, stream>>>(p); break;
   switch (b->variant) {
     EKF_BATCH_CASE(0, 16, false, 0)  EKF_BATCH_CASE(1, 16, false, 1)  EKF_BATCH_CASE(2, 16, false, 2)
     EKF_BATCH_CASE(4, 16, true, 0)   EKF_BATCH_CASE(5, 16, true, 1)   EKF_BATCH_CASE(6, 16, true, 2)
@@ -105,6 +113,11 @@ int ekf_batch_destroy(ekf_batch *b) {
     if (b->io_host) cudaFreeHost(b->io_host);
     if (b->res_host) cudaFreeHost(b->res_host);
     if (b->own_stream) cudaStreamDestroy(b->own_stream);
+    for (int q = 0; q < 2; ++q) {
+      if (b->side[q]) cudaStreamDestroy(b->side[q]);
+      if (b->ev_side[q]) cudaEventDestroy(b->ev_side[q]);
+    }
+    if (b->ev_begin) cudaEventDestroy(b->ev_begin);
   }
   delete b;
   return EKF_OK;
@@ -134,6 +147,17 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
 #define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(e_, #call); } while (0)
   CKC(cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking));
   b->stream = b->own_stream;
+  for (int q = 0; q < 2; ++q) {
+    CKC(cudaStreamCreateWithFlags(&b->side[q], cudaStreamNonBlocking));
+    CKC(cudaEventCreateWithFlags(&b->ev_side[q], cudaEventDisableTiming));
+  }
+  CKC(cudaEventCreateWithFlags(&b->ev_begin, cudaEventDisableTiming));
+  b->chunks = 1;
+  if (b->B >= 4096) b->chunks = 8;
+  if (const char *v = getenv("EKF_BATCH_CHUNKS")) b->chunks = atoi(v);
+  if (b->chunks < 1) b->chunks = 1;
+  if (b->chunks > 64) b->chunks = 64;
+  if (b->chunks > b->B) b->chunks = b->B;
   const size_t sig_bytes = (size_t)b->B * b->tri * sizeof(double);
   CKC(cudaMalloc(&b->sigma, sig_bytes));
   CKC(cudaMalloc(&b->mu, (size_t)b->B * b->n * sizeof(double)));
@@ -261,6 +285,44 @@ int ekf_batch_step(ekf_batch *b, const double *poses, int32_t m, const double *x
     return a.type == cudaMemoryTypeHost;
   };
   const bool in_direct = pinned(poses) && pinned(xy) && (!ids || pinned(ids)) && (!m_count || pinned(m_count));
+  const bool out_direct = (!out_assoc || pinned(out_assoc)) && (!out_count || pinned(out_count)) &&
+                          (!out_pose || pinned(out_pose));
+  double *const d_pose = reinterpret_cast<double *>(b->io_dev + io.pose);
+  double *const d_xy = reinterpret_cast<double *>(b->io_dev + io.xy);
+  int32_t *const d_ids = ids ? reinterpret_cast<int32_t *>(b->io_dev + io.ids) : nullptr;
+  int32_t *const d_mc = m_count ? reinterpret_cast<int32_t *>(b->io_dev + io.mc) : nullptr;
+  int32_t *const r_assoc = reinterpret_cast<int32_t *>(b->res_dev + io.r_assoc);
+  int32_t *const r_cnt = reinterpret_cast<int32_t *>(b->res_dev + io.r_cnt);
+  double *const r_pose = reinterpret_cast<double *>(b->res_dev + io.r_pose);
+  if (in_direct && out_direct && b->chunks > 1) {
+    // chunked pipeline over two side streams (copy engines for the two directions and the SMs all busy at once);
+    // every per-filter array is contiguous in filters, so a chunk is one slice of each
+    CKB(b, cudaEventRecord(b->ev_begin, b->stream));
+    for (int q = 0; q < 2; ++q) CKB(b, cudaStreamWaitEvent(b->side[q], b->ev_begin, 0));
+    for (int c = 0; c < b->chunks; ++c) {
+      const size_t f0 = B * c / b->chunks, f1 = B * (c + 1) / b->chunks, nf = f1 - f0;
+      cudaStream_t st = b->side[c & 1];
+      CKB(b, cudaMemcpyAsync(d_pose + 3 * f0, poses + 3 * f0, 24 * nf, cudaMemcpyHostToDevice, st));
+      CKB(b, cudaMemcpyAsync(d_xy + 2 * f0 * m, xy + 2 * f0 * m, 16 * nf * m, cudaMemcpyHostToDevice, st));
+      if (ids) CKB(b, cudaMemcpyAsync(d_ids + f0 * m, ids + f0 * m, 4 * nf * m, cudaMemcpyHostToDevice, st));
+      if (m_count) CKB(b, cudaMemcpyAsync(d_mc + f0, m_count + f0, 4 * nf, cudaMemcpyHostToDevice, st));
+      rc = batch_launch(b, d_pose, m, d_xy, d_ids, d_mc, r_assoc, r_cnt, r_pose, (int)f0, (int)nf, st);
+      if (rc != EKF_OK) return rc;
+      if (out_assoc) CKB(b, cudaMemcpyAsync(out_assoc + f0 * m, r_assoc + f0 * m, 4 * nf * m, cudaMemcpyDeviceToHost, st));
+      if (out_count) CKB(b, cudaMemcpyAsync(out_count + f0, r_cnt + f0, 4 * nf, cudaMemcpyDeviceToHost, st));
+      if (out_pose) CKB(b, cudaMemcpyAsync(out_pose + 3 * f0, r_pose + 3 * f0, 24 * nf, cudaMemcpyDeviceToHost, st));
+    }
+    for (int q = 0; q < 2; ++q) {
+      CKB(b, cudaEventRecord(b->ev_side[q], b->side[q]));
+      CKB(b, cudaStreamWaitEvent(b->stream, b->ev_side[q], 0));
+    }
+    CKB(b, cudaMemcpyAsync(b->res_host + io.r_status, b->status, sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+    CKB(b, cudaMemsetAsync(b->status, 0, sizeof(int), b->stream));
+    CKB(b, cudaStreamSynchronize(b->stream));
+    int st_chunked = 0;
+    memcpy(&st_chunked, b->res_host + io.r_status, 4);
+    return st_chunked;
+  }
   if (in_direct) {
     CKB(b, cudaMemcpyAsync(b->io_dev + io.pose, poses, 24 * B, cudaMemcpyHostToDevice, b->stream));
     CKB(b, cudaMemcpyAsync(b->io_dev + io.xy, xy, 16 * B * m, cudaMemcpyHostToDevice, b->stream));
@@ -273,18 +335,10 @@ int ekf_batch_step(ekf_batch *b, const double *poses, int32_t m, const double *x
     if (m_count) memcpy(b->io_host + io.mc, m_count, 4 * B);
     CKB(b, cudaMemcpyAsync(b->io_dev, b->io_host, io.total, cudaMemcpyHostToDevice, b->stream));
   }
-  rc = batch_launch(b, reinterpret_cast<const double *>(b->io_dev + io.pose), m,
-                    reinterpret_cast<const double *>(b->io_dev + io.xy),
-                    ids ? reinterpret_cast<const int32_t *>(b->io_dev + io.ids) : nullptr,
-                    m_count ? reinterpret_cast<const int32_t *>(b->io_dev + io.mc) : nullptr,
-                    reinterpret_cast<int32_t *>(b->res_dev + io.r_assoc),
-                    reinterpret_cast<int32_t *>(b->res_dev + io.r_cnt),
-                    reinterpret_cast<double *>(b->res_dev + io.r_pose));
+  rc = batch_launch(b, d_pose, m, d_xy, d_ids, d_mc, r_assoc, r_cnt, r_pose);
   if (rc != EKF_OK) return rc;
   CKB(b, cudaMemcpyAsync(b->res_dev + io.r_status, b->status, sizeof(int), cudaMemcpyDeviceToDevice, b->stream));
   CKB(b, cudaMemsetAsync(b->status, 0, sizeof(int), b->stream));
-  const bool out_direct = (!out_assoc || pinned(out_assoc)) && (!out_count || pinned(out_count)) &&
-                          (!out_pose || pinned(out_pose));
   if (out_direct) {
     if (out_assoc) CKB(b, cudaMemcpyAsync(out_assoc, b->res_dev + io.r_assoc, 4 * B * m, cudaMemcpyDeviceToHost, b->stream));
     if (out_count) CKB(b, cudaMemcpyAsync(out_count, b->res_dev + io.r_cnt, 4 * B, cudaMemcpyDeviceToHost, b->stream));

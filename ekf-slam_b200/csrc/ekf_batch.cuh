@@ -25,6 +25,7 @@ namespace ekf {
 
 struct BatchParams {
   int B, N, n, tri;
+  int f0;                  // first filter of this launch (CTA b works on filter f0 + b; chunked host-buffer steps)
   double q_noise, r_noise, thr;
   double *sigma, *mu, *prev;
   int *cnt;
@@ -117,6 +118,31 @@ __device__ __forceinline__ void dmma884_b(double &c0, double &c1, double a, doub
                : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// Sigma -= K G^T over the NT (NT + 1) / 2 stored 8x8 tiles, fully unrolled for a compile-time tile count: the G
+// fragments of all block-columns stay in registers, every tile is one 128-bit load, one DMMA and one 128-bit store at
+// a constant offset (the generic loop spends more instructions on its counters and fragment reloads than on tiles)
+template <int NT>
+__device__ __forceinline__ void batch_downdate_tiles(double *S, const double2 *K, const double2 *G, int lane) {
+  const int fr = lane >> 2, fk = lane & 3;
+  const double *Kd = reinterpret_cast<const double *>(K), *Gd = reinterpret_cast<const double *>(G);
+  double2 *t0 = reinterpret_cast<double2 *>(S) + batch_tile_chunk(0, fr, fk);
+  double2 *t1 = reinterpret_cast<double2 *>(S) + batch_tile_chunk(1, fr, fk);
+  double bJ[NT];
+#pragma unroll
+  for (int J = 0; J < NT; ++J) bJ[J] = fk < 2 ? Gd[(8 * J + fr) * 2 + fk] : 0.0;
+#pragma unroll
+  for (int I = 0; I < NT; ++I) {
+    const double aI = fk < 2 ? -Kd[(8 * I + fr) * 2 + fk] : 0.0;
+    double2 *ct = ((I & 1) ? t1 : t0) + 32 * (I * (I + 1) / 2);
+#pragma unroll
+    for (int J = 0; J <= I; ++J) {
+      double2 c = ct[32 * J];
+      dmma884_b(c.x, c.y, aI, bJ[J]);
+      ct[32 * J] = c;
+    }
+  }
+}
+
 template <int MINB, bool ONEPASS, int DD>
 __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const BatchParams p) {
   extern __shared__ __align__(16) double sm[];
@@ -129,7 +155,7 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
   double2 *K = G + gk;                                          // K = G S^-1      (n x 2)
   double *ZP = reinterpret_cast<double *>(K + gk);              // polar sightings (m x 2)
   auto g_at = [&](int j) { return DD == 1 ? batch_g_idx(j, half) : j; };
-  const int f = blockIdx.x;
+  const int f = p.f0 + blockIdx.x;
   const int lane = threadIdx.x;
   if (f >= p.B) return;
 
@@ -200,6 +226,19 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
     ZP[2 * t] = z.r; ZP[2 * t + 1] = z.phi;
   }
   __syncwarp();
+  // shared-memory offsets that do not change from one measurement to the next (the swizzled tile layout makes each a
+  // dozen integer instructions): the lane's own candidate (ONEPASS: candidate k == lane) and the pose-panel entries of
+  // the rows the lane owns in the G / K sweep (rows lane and lane + 32)
+  int c_a0 = 0, c_a2 = 0, c_b0 = 0, c_b2 = 0, c_aa = 0, c_ba = 0, c_bb = 0;
+  if constexpr (ONEPASS) {
+    const int a = 3 + 2 * min(lane, p.N - 1);
+    c_a0 = batch_s_idx<DD>(a, 0); c_a2 = batch_s_idx<DD>(a, 2);
+    c_b0 = batch_s_idx<DD>(a + 1, 0); c_b2 = batch_s_idx<DD>(a + 1, 2);
+    c_aa = batch_s_idx<DD>(a, a); c_ba = batch_s_idx<DD>(a + 1, a); c_bb = batch_s_idx<DD>(a + 1, a + 1);
+  }
+  const int g_i0 = min(lane, n - 1), g_i1 = min(lane + 32, n - 1);
+  const int g00 = tri_idx<DD>(g_i0, 0), g01 = tri_idx<DD>(g_i0, 1), g02 = tri_idx<DD>(g_i0, 2);
+  const int g10 = tri_idx<DD>(g_i1, 0), g11 = tri_idx<DD>(g_i1, 1), g12 = tri_idx<DD>(g_i1, 2);
   for (int t = 0; t < mf; ++t) {
     const Polar z{ZP[2 * t], ZP[2 * t + 1]};
     const double th = mu[0], px = mu[1], py = mu[2];
@@ -223,12 +262,14 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
              r_z1 = 0.0;
       for (int k = lane; k < cnt; k += 32) {                   // slam.cpp:361-404 (ONEPASS: at most one trip)
         // columns 0, 1 of a row are adjacent in both layouts; everything else is looked up
-        const int a = 3 + 2 * k, ra = batch_s_idx<DD>(a, 0), rb = batch_s_idx<DD>(a + 1, 0);
-        const double pa[3] = {S[ra], S[ra + 1], S[batch_s_idx<DD>(a, 2)]},
-                     pbr[3] = {S[rb], S[rb + 1], S[batch_s_idx<DD>(a + 1, 2)]};
+        const int a = 3 + 2 * k;
+        const int ra = ONEPASS ? c_a0 : batch_s_idx<DD>(a, 0), rb = ONEPASS ? c_b0 : batch_s_idx<DD>(a + 1, 0);
+        const double pa[3] = {S[ra], S[ra + 1], S[ONEPASS ? c_a2 : batch_s_idx<DD>(a, 2)]},
+                     pbr[3] = {S[rb], S[rb + 1], S[ONEPASS ? c_b2 : batch_s_idx<DD>(a + 1, 2)]};
         const Lin Lk = linearize(th, px, py, mu[a], mu[a + 1]);
-        const Block5 Bk = make_block5(pb, pa, pbr, S[batch_s_idx<DD>(a, a)], S[batch_s_idx<DD>(a + 1, a)],
-                                      S[batch_s_idx<DD>(a + 1, a + 1)]);
+        const Block5 Bk = make_block5(pb, pa, pbr, S[ONEPASS ? c_aa : batch_s_idx<DD>(a, a)],
+                                      S[ONEPASS ? c_ba : batch_s_idx<DD>(a + 1, a)],
+                                      S[ONEPASS ? c_bb : batch_s_idx<DD>(a + 1, a + 1)]);
         const Innov I = innovation(Bk, Lk, p.r_noise);
         const double z0 = z.r - Lk.zhat_r, z1 = normalize_angle(z.phi - Lk.zhat_b);
         double i00, i01, i11;
@@ -248,7 +289,23 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
           best = nb;
         }
       }
-      best = warp_argmin(best);
+      if constexpr (ONEPASS) {
+        // candidate k sits in lane k, so "lowest index on ties" is "lowest lane": arg-min of the 64-bit order key of
+        // the distance with two 32-bit warp reductions and a ballot instead of five shuffle rounds.  The key is the
+        // usual monotone map of IEEE doubles onto unsigned integers (exact for every non-NaN value; a NaN distance
+        // never became `best`, slam.cpp:418); + 0.0 folds -0.0 into +0.0, which compare equal in the reference
+        const unsigned long long bits = (unsigned long long)__double_as_longlong(best.d + 0.0);
+        const unsigned long long key = bits ^ ((bits >> 63) ? ~0ULL : 0x8000000000000000ULL);
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mhi = __reduce_min_sync(0xffffffffu, hi);
+        const unsigned mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+        const unsigned win = __ballot_sync(0xffffffffu, hi == mhi && lo == mlo);
+        const int src = __ffs(win) - 1;
+        best.d = __shfl_sync(0xffffffffu, best.d, src);
+        best.k = __shfl_sync(0xffffffffu, best.k, src);
+      } else {
+        best = warp_argmin(best);
+      }
       if (best.d <= p.thr && best.k < cnt) {                   // slam.cpp:406-408,418-440
         j = best.k;
         const int src = j & 31;                                // candidate k lives in lane k % 32
@@ -293,9 +350,9 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
     __syncwarp();
     if (is_new && lane == 0) { mu[a] = lx; mu[a + 1] = ly; }
     __syncwarp();
-    for (int i = lane; i < n; i += 32) {                       // G = Sigma H^T, K = G S^-1, state
-      const double row[5] = {S[tri_idx<DD>(i, 0)], S[tri_idx<DD>(i, 1)], S[tri_idx<DD>(i, 2)], S[tri_idx<DD>(i, a)],
-                             S[tri_idx<DD>(i, a + 1)]};
+    // G = Sigma H^T, K = G S^-1, state: one row per lane and trip; the first two trips use the hoisted offsets
+    auto gk_row = [&](int i, int o0, int o1, int o2) {
+      const double row[5] = {S[o0], S[o1], S[o2], S[tri_idx<DD>(i, a)], S[tri_idx<DD>(i, a + 1)]};
       double g0, g1;
       row_times_ht(row, L, g0, g1);
       const double k0 = g0 * m00 + g1 * m01, k1 = g0 * m01 + g1 * m11;
@@ -304,7 +361,10 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
       double v = mu[i] + (k0 * zd0 + k1 * zd1);                // slam.cpp:482
       if (i == 0) v = normalize_angle(v);                      // slam.cpp:488
       mu[i] = v;
-    }
+    };
+    if (lane < n) gk_row(lane, g00, g01, g02);
+    if (lane + 32 < n) gk_row(lane + 32, g10, g11, g12);
+    for (int i = lane + 64; i < n; i += 32) gk_row(i, tri_idx<DD>(i, 0), tri_idx<DD>(i, 1), tri_idx<DD>(i, 2));
     __syncwarp();
     // Sigma -= K G^T on the stored triangle, element by element in packed order: 32 consecutive
     // elements per step keep every lane busy (a column-per-lane walk idles half of them on the triangle);
@@ -313,6 +373,9 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
       // C tile (accumulator order in shared memory) += (-K rows of block-row I) x (G rows of block-column J)^T;
       // fragment element (row lane / 4, k = lane % 4): k = 0, 1 are the two columns of K / G, k = 2, 3 are zero
       const int nt = (n + 7) >> 3, fr = lane >> 2, fk = lane & 3;
+      if (nt == 6) {                       // n = 41 .. 48: BASELINE config 3 (N = 20, n = 43)
+        batch_downdate_tiles<6>(S, K, G, lane);
+      } else {
       const double *Kd = reinterpret_cast<const double *>(K), *Gd = reinterpret_cast<const double *>(G);
       const double2 *tile = reinterpret_cast<const double2 *>(S);
       const int ch[2] = {batch_tile_chunk(0, fr, fk), batch_tile_chunk(1, fr, fk)};   // this lane's chunk, even / odd I
@@ -326,6 +389,7 @@ __global__ void __launch_bounds__(kBatchThreads, MINB) ekf_batch_kernel(const Ba
           *ct = c;
         }
         tile += 32 * (I + 1);
+      }
       }
     } else if constexpr (DD == 1) {
       // 2x2 blocks: two K rows and two G columns serve up to four elements.  K[n] / G[n] of an odd n are read

@@ -79,3 +79,33 @@ def test_replay_bag_program_matches_oracle_a(tmp_path):
     assert [[int(v) for v in r.split()[5:]] for r in rows[:-1]] == [list(map(int, a)) for a in aL]
     last = rows[-2].split()
     assert np.allclose([float(v) for v in last[1:4]], sL[:3], rtol=0, atol=1e-9) and int(last[4]) == cL
+
+
+def _build_shard_replay(tmp_path, nccl=False):
+    exe = str(tmp_path / "shard_replay")
+    pkg = os.path.join(ROOT, "ekf-slam_b200")
+    cmd = ["nvcc", "-x", "cu", "-std=c++17", "-O2", "-gencode", "arch=compute_100a,code=sm_100a",
+           "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tools", "shard_replay.cpp"), "-o", exe,
+           "-L" + pkg, "-lekf_slam_b200", "-Xlinker", "-rpath=" + pkg]
+    if nccl:
+        cmd += ["-DSHARD_REPLAY_NCCL", "-lnccl"]
+    subprocess.check_call(cmd)
+    return exe
+
+
+@pytest.mark.parametrize("shards,extra", [(3, []), (2, ["--allreduce"]), (4, ["--m", "24"])])
+def test_cpp_multi_gpu_host_loop_on_the_c_abi(tmp_path, shards, extra):
+    """tools/shard_replay.cpp (INTEGRATION.md section 10 as a program): R row-shard handles driven from C++ on
+    the C ABI - peer-memory exchange or summed buffers - against the unsharded filter on the same scans.  On a
+    one-GPU box the R handles share the device; with R <= devices it is one shard per GPU."""
+    import json
+    if not os.path.exists(ekf_slam_b200.LIB_PATH):
+        ekf_slam_b200.build()
+    exe = _build_shard_replay(tmp_path)
+    out = subprocess.run([exe, "--shards", str(shards), "--landmarks", "1500", "--scans", "6"] + extra,
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    d = json.loads(out.stdout.strip().splitlines()[-1])
+    assert d["ok"] and d["association_as_expected"] and d["association_equals_unsharded"] and d["replicas_bitwise_equal"]
+    assert d["state_rel_vs_unsharded"] <= 1e-12 and d["sigma_rel_vs_unsharded"] <= 1e-12
+    assert d["rounds"] == 6
