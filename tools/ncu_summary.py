@@ -28,6 +28,14 @@ METRICS = [
     "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__inst_executed_pipe_fp64_op_dmma.sum", "sm__inst_executed_pipe_fp64_op_dmma.avg.pct_of_peak_sustained_active",
     "smsp__inst_executed_op_dmma.sum",
+    # fp64 tensor sub-pipe (DMMA) busy cycles per SM sub-partition: divide by smsp__cycles_active.avg for the
+    # "DMMA pipe x % of its cycles active" figure DESIGN.md quotes (listed as SM_C.TriageCompute.<name>)
+    "smsp__pipe_tensor_subpipe_dmma_cycles_active.avg",
+    "sm__inst_executed_pipe_fp64.sum.pct_of_peak_sustained_active",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
+    "derived__memory_l1_wavefronts_shared_excessive",
+    "smsp__thread_inst_executed_per_inst_executed.ratio",
     "sm__sass_thread_inst_executed_op_dfma_pred_on.sum", "sm__sass_thread_inst_executed_op_dmul_pred_on.sum",
     "sm__sass_thread_inst_executed_op_dadd_pred_on.sum",
     "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
@@ -49,6 +57,9 @@ def main():
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units, launches = rows[0], rows[1], rows[2:]
     idx = {n: i for i, n in enumerate(hdr)}
+    for n, i in list(idx.items()):           # "SM_C.TriageCompute.<metric>" -> also reachable as "<metric>"
+        if ".Triage" in n:
+            idx.setdefault(n.split(".", 2)[2], i)
     out = csv.writer(sys.stdout, lineterminator="\n")
     if note:
         print("# " + note)
