@@ -32,6 +32,8 @@ struct ekf_filter {
   EkfLay lay{0, 0};        // rows of Sigma this handle stores (whole matrix unless row-sharded)
   bool sharded = false;
   bool side_valid = false; // sharded: Pp / D replicated and current
+  bool side_dirty = false; // sharded: Pp / D are NEWER than the Sigma entries they mirror (written back lazily)
+  const double *pend_pose = nullptr;   // the round opened by ekf_shard_scan_begin predicts from this pose (or nullptr)
   double *cols = nullptr;  // sharded: exchange buffer, kMaxChunkM x n_pad x 2
   int *guess = nullptr;    // sharded: speculative association of the round
   int *done_dev = nullptr; // sharded: measurements processed by the last finish

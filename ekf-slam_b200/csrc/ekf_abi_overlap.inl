@@ -35,7 +35,15 @@ int shard_buffers(ekf_filter *f) {
 }
 
 // Back to the single-buffer state every other entry point expects.  Cheap when nothing is in flight.
-int pipe_drain(ekf_filter *f) {
+int pipe_drain(ekf_filter *f, bool keep_side = false) {
+  // the shard protocol keeps the pose panel / diagonal blocks current in Pp / D only; everything that reads or
+  // rewrites Sigma gets them written back first (keep_side: the next shard round, which does not read them there)
+  if (f->side_dirty && !keep_side && !f->pipe_active) {
+    shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
+    f->launches++;
+    CK(f, cudaGetLastError());
+    f->side_dirty = false;
+  }
   if (!f->pipe_active) return EKF_OK;
   const int64_t k = f->pipe_step;                       // rounds issued: passes 0 .. k-1 are queued on B
   CK(f, cudaStreamWaitEvent(f->stream, f->ev_pass[(k - 1) & 1], 0));
@@ -46,6 +54,7 @@ int pipe_drain(ekf_filter *f) {
   shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
   f->launches++;
   CK(f, cudaGetLastError());
+  f->side_dirty = false;
   f->pipe_active = false;
   f->pipe_step = 0;
   f->pipe_k2_prev = 0;

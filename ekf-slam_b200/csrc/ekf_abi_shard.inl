@@ -99,43 +99,45 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
   if (!shard_ok(f) || m < 1 || !xy_dev || !xchg_dev || !xchg_doubles) return EKF_ERR_INVALID;
   if (!f->side_valid) return EKF_ERR_INVALID;        // ekf_shard_sync_begin / _finish first
   DeviceGuard guard(f->device);
-  { const int rcd = pipe_drain(f); if (rcd != EKF_OK) return rcd; }
+  { const int rcd = pipe_drain(f, /*keep_side=*/true); if (rcd != EKF_OK) return rcd; }
   const int mc = m < kMaxChunkM ? m : kMaxChunkM;    // a round handles at most kMaxChunkM sightings
-  if (pose_dev) {
-    shard_predict_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->Pp, f->mu, pose_dev, f->prev_xy, f->N,
-                                                            f->cfg.q_noise);
-    f->launches++;
-  }
   int slices = (2 * f->num_sms + mc - 1) / mc;        // about two CTAs per SM in total
   const int useful = (f->N + kGuessThreads - 1) / kGuessThreads;
   if (slices > useful) slices = useful;
   if (slices > kGuessMaxSlices) slices = kGuessMaxSlices;
   if (slices < 1) slices = 1;
-  shard_guess_kernel<<<dim3(mc, slices), kGuessThreads, 0, f->stream>>>(
-      f->Pp, f->D, f->mu, f->cnt, xy_dev, ids_dev, f->guess, f->cfg.r_noise, f->cfg.mah_threshold, f->guess_part_d,
-      f->guess_part_k, f->guess_ticket);
-  // test-only fault injection: forget the speculation for one sighting so that the stop / resume path runs
-  const int drop = env_int("EKF_SHARD_DROP_GUESS", -1);
-  if (drop >= 0 && drop < mc) CK(f, cudaMemsetAsync(f->guess + drop, 0xFF, sizeof(int), f->stream));
   f->pend_peer = shard_peer_mode(f) ? 1 : 0;
+  // ONE kernel: the prediction is applied on the fly (the sequential kernel applies it to the replicated Pp when it
+  // starts), the last CTA of every sighting delivers its landmark's columns to every rank (peer mode)
+  BeginParams bp{};
+  bp.Pp = f->Pp; bp.D = f->D; bp.mu = f->mu; bp.cnt = f->cnt;
+  bp.pose = pose_dev; bp.prev_xy = f->prev_xy;
+  bp.q_noise = f->cfg.q_noise; bp.r_noise = f->cfg.r_noise; bp.thr = f->cfg.mah_threshold;
+  bp.xy = xy_dev; bp.ids = ids_dev; bp.guess = f->guess;
+  bp.part_d = f->guess_part_d; bp.part_k = f->guess_part_k; bp.ticket = f->guess_ticket;
+  bp.drop = env_int("EKF_SHARD_DROP_GUESS", -1);       // test-only fault injection (stop / resume path)
+  if (bp.drop >= mc) bp.drop = -1;
+  bp.push = f->pend_peer;
+  bp.sigma = f->sigma; bp.lay = f->lay; bp.n_pad = f->n_pad; bp.N = f->N;
   if (f->pend_peer) {
-    // extraction + exchange + arrival flags in one kernel over peer memory: nothing left for the caller
     f->xchg_round++;
-    PeerTable pt{};
-    pt.count = f->cfg.shard_count; pt.self = f->cfg.shard_rank;
+    bp.peers.count = f->cfg.shard_count; bp.peers.self = f->cfg.shard_rank;
     const size_t par_off = (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes;
-    for (int q = 0; q < pt.count; ++q) {
-      pt.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
-      pt.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
+    for (int q = 0; q < bp.peers.count; ++q) {
+      bp.peers.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
+      bp.peers.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
     }
-    shard_push_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt,
-                                                                  f->xchg_round, f->push_done);
-  } else {
+    bp.round_no = f->xchg_round; bp.done_slots = f->push_done;
+  }
+  shard_begin_kernel<<<dim3(mc, slices), kGuessThreads, 0, f->stream>>>(bp);
+  f->launches++;
+  if (!f->pend_peer) {
     shard_extract_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc,
                                                                      f->cols);
+    f->launches++;
   }
-  f->launches += 2;
   CK(f, cudaGetLastError());
+  f->pend_pose = pose_dev;
   f->pend_m = mc; f->pend_xy = xy_dev; f->pend_ids = ids_dev;
   f->pend_finish = (last_round && mc == m) ? 1 : 0;
   *xchg_dev = f->pend_peer ? nullptr : f->cols;
@@ -163,8 +165,8 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   sp.q_noise = f->cfg.q_noise; sp.r_noise = f->cfg.r_noise; sp.thr = f->cfg.mah_threshold;
   sp.sigma = f->sigma; sp.mu = f->mu; sp.Pp = f->Pp; sp.D = f->D; sp.W = f->W; sp.V = f->V;
   sp.cnt = f->cnt; sp.prev_xy = f->prev_xy; sp.status = f->status;
-  sp.pose = nullptr; sp.xy = f->pend_xy; sp.ids = f->pend_ids; sp.action = nullptr;
-  sp.m = mc; sp.do_predict = 0; sp.finish = f->pend_finish;
+  sp.pose = f->pend_pose; sp.xy = f->pend_xy; sp.ids = f->pend_ids; sp.action = nullptr;
+  sp.m = mc; sp.do_predict = f->pend_pose != nullptr ? 1 : 0; sp.finish = f->pend_finish;
   sp.assoc_out = assoc_dev;
   sp.pose_out = pose_out_dev ? pose_out_dev : reinterpret_cast<double *>(f->res_dev + res.pose);
   sp.cnt_out = count_dev ? count_dev : reinterpret_cast<int *>(f->res_dev + res.cnt);
@@ -172,10 +174,10 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   if (f->pend_peer) {
     // every rank's part of this round must have landed in this rank's buffer before it is read
     sp.cols = reinterpret_cast<const double *>(f->xchg + (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes);
-    shard_wait_peers_kernel<<<1, 32, 0, f->stream>>>(
-        reinterpret_cast<const unsigned long long *>(f->xchg + 2 * f->xchg_cols_bytes), f->cfg.shard_count,
-        f->xchg_round, f->status);
-    f->launches++;
+    // ... which the sequential kernel waits for itself, after its prologue (no separate wait kernel)
+    sp.wait_flags = reinterpret_cast<const unsigned long long *>(f->xchg + 2 * f->xchg_cols_bytes);
+    sp.wait_count = f->cfg.shard_count;
+    sp.wait_round = f->xchg_round;
   }
   sp.done_out = done_dev ? done_dev : f->done_dev;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
@@ -184,6 +186,7 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   if (hot) { sp.hot_hdr = f->hot_hdr; sp.hot_rec = f->hot_rec; sp.hot_w = f->hot_w; }
   f->bar_base += (unsigned long long)mc * (unsigned long long)f->seq_grid;
   f->pend_m = -1;
+  f->pend_pose = nullptr;
 
   const bool timed = f->ev_cap > 0;
   const size_t slot = timed ? (size_t)(f->ev_count % f->ev_cap) * 4 : 0;
@@ -208,8 +211,10 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   long long grid = f->dd_grid;
   if (grid > dp.total_chunks) grid = dp.total_chunks;
   ekf_downdate_kernel<64, 2><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
-  shard_side_writeback_kernel<<<f->num_sms, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->Pp, f->D);
-  f->launches += 2;
+  // Pp / D now hold the current pose panel / diagonal blocks; the Sigma entries they mirror (which the pass has
+  // just recomputed with its own rounding) are written back lazily, by whatever reads or rewrites Sigma next
+  f->side_dirty = true;
+  f->launches += 1;
   CK(f, cudaGetLastError());
   if (timed) { CK(f, cudaEventRecord(f->ev[slot + 3], f->stream)); f->ev_count++; }
   return EKF_OK;

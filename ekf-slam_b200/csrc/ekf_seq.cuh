@@ -97,6 +97,11 @@ struct SeqParams {
   const double *cols;
   const int *guess;
   int *done_out;          // measurements actually processed (a failed speculation stops the scan early)
+  // peer-memory exchange: the columns of this round are complete once every rank's arrival flag has reached
+  // wait_round (ekf_shard.cuh); the kernel waits for them itself, after its prologue (nullptr: nothing to wait for)
+  const unsigned long long *wait_flags;
+  int wait_count;
+  unsigned long long wait_round;
   // grid barrier + arg-min slots
   unsigned long long *bar;
   unsigned long long bar_base;
@@ -297,7 +302,19 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
   // every update (thread 0's serial path and the next launch read them) but never re-read by the owner.
   double4 o_pa = make_double4(0.0, 0.0, 0.0, 0.0), o_pb = o_pa, o_dk = o_pa;
   double2 o_lm = make_double2(0.0, 0.0);
-  if (p.side_mode && gtid < p.N) {
+  if (p.side_mode && p.do_predict) {
+    // the prediction on the replicated pose panel (no separate kernel on the sharded path): slam.cpp:194-198
+    const double ndy = s_pred[0], pdx = s_pred[1];
+    for (int k = gtid; k < p.N; k += nthreads_total) {
+      const int a = 4 + 2 * k;
+      double4 va = p.Pp[a], vb = p.Pp[a + 1];
+      va.y = va.x * ndy + va.y; va.z = va.x * pdx + va.z;
+      vb.y = vb.x * ndy + vb.y; vb.z = vb.x * pdx + vb.z;
+      p.Pp[a] = va; p.Pp[a + 1] = vb;
+      if (k == gtid) { o_pa = va; o_pb = vb; }
+    }
+    if (gtid < p.N) o_dk = p.D[gtid];
+  } else if (p.side_mode && gtid < p.N) {
     o_pa = p.Pp[4 + 2 * gtid]; o_pb = p.Pp[5 + 2 * gtid]; o_dk = p.D[gtid];
   }
   if (gtid < p.N) o_lm = *reinterpret_cast<const double2 *>(p.mu + 4 + 2 * gtid);
@@ -321,6 +338,22 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
       p.D[k] = make_double4(d0.x, d1.x, d1.y, 0.0);
       if (k == gtid) { o_pa = va; o_pb = vb; o_dk = make_double4(d0.x, d1.x, d1.y, 0.0); }
     }
+  }
+
+  // the exchanged columns of this round: every rank's arrival flag (system-scope acquire; bounded like
+  // shard_wait_peers_kernel - a peer that never arrives latches EKF_ERR_CUDA after ~10 s instead of hanging)
+  if (p.wait_flags != nullptr) {
+    if (tid < p.wait_count) {
+      unsigned long long t0, now, v;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      for (;;) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p.wait_flags + tid) : "memory");
+        if (v >= p.wait_round) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 >= 10000000000ull) { atomicMax(p.status, kErrCuda); break; }
+      }
+    }
+    __syncthreads();
   }
 
   // ---------------- measurement loop --------------------------------------------------------

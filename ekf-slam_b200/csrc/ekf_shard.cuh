@@ -269,6 +269,171 @@ __global__ void shard_wait_peers_kernel(const unsigned long long *flags, int cou
   atomicMax(status, kErrPeerTimeout);
 }
 
+// ---- the whole begin phase as ONE kernel (peer mode): prediction on the fly + speculative association + delivery ----
+// Replaces shard_predict_kernel + shard_guess_kernel + shard_push_cols_kernel (three launches, ~0.05 ms of launch
+// gaps and ramps at 8 GPUs) on the per-scan path:
+//   * the prediction is not applied here at all: every candidate's pose-panel rows and the pose block are
+//     transformed in registers (slam.cpp:194-198 restricted to the n x 3 panel) - the sequential kernel applies
+//     the same transform to the replicated Pp when it starts (SeqParams::do_predict with side_mode);
+//   * the last CTA of a sighting to finish (ticket) reduces the slices' candidates to guess[t] and then DELIVERS:
+//     it stores the part this rank owns of the raw Sigma_0 columns of that landmark into every rank's buffer;
+//   * the last of those m delivering CTAs raises this rank's arrival flag everywhere (system-scope release).
+struct BeginParams {
+  const double4 *Pp, *D;
+  const double *mu;
+  const int *cnt;
+  const double *pose;        // device (theta, x, y); nullptr = continuation round, no prediction
+  const double *prev_xy;
+  double q_noise, r_noise, thr;
+  const double *xy;
+  const int *ids;
+  int *guess;
+  double *part_d;
+  int *part_k;
+  unsigned int *ticket;
+  int drop;                  // test-only fault injection: forget the speculation of this sighting (-1 = none)
+  int push;                  // 1: deliver through peer memory here; 0: the caller extracts and all-reduces
+  const double *sigma;
+  EkfLay lay;
+  int n_pad, N;
+  PeerTable peers;
+  unsigned long long round_no;
+  unsigned int *done_slots;
+};
+
+// A P A^T + Qbar on the 3 x 3 pose block, lower triangle rules (the arithmetic of shard_predict_kernel / phase 0 of
+// ekf_seq_kernel); ndy = -dy, pdx = dx
+__device__ __forceinline__ void predict_block3(double P[3][3], double ndy, double pdx, double q_noise) {
+  double Bm[3][3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < i; ++j) P[j][i] = P[i][j];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    Bm[0][j] = P[0][j];
+    Bm[1][j] = ndy * P[0][j] + P[1][j];
+    Bm[2][j] = pdx * P[0][j] + P[2][j];
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    P[i][0] = Bm[i][0];
+    P[i][1] = Bm[i][0] * ndy + Bm[i][1];
+    P[i][2] = Bm[i][0] * pdx + Bm[i][2];
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) P[i][i] += q_noise;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < i; ++j) P[j][i] = P[i][j];
+}
+
+__global__ void __launch_bounds__(kGuessThreads) shard_begin_kernel(const BeginParams p) {
+  __shared__ Cand s_red[kGuessThreads / 32];
+  __shared__ int s_last, s_guess;
+  __shared__ unsigned int s_prev;
+  const int t = blockIdx.x, slice = blockIdx.y, P = gridDim.y;
+  if (p.ids != nullptr) {                                  // known association: nothing to speculate
+    if (slice != 0) return;
+    if (threadIdx.x == 0) { s_guess = p.ids[t]; p.guess[t] = s_guess; s_last = 1; }
+  } else {
+    const int cnt = *p.cnt;
+    const Polar z = to_polar(p.xy[2 * t], p.xy[2 * t + 1]);
+    double th = p.mu[0], px = p.mu[1], py = p.mu[2], ndy = 0.0, pdx = 0.0;
+    double pb[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double4 r = p.Pp[i];
+      pb[i][0] = r.x; pb[i][1] = r.y; pb[i][2] = r.z;
+    }
+    const bool pred = p.pose != nullptr;
+    if (pred) {
+      th = normalize_angle(p.pose[0]); px = p.pose[1]; py = p.pose[2];          // slam.cpp:186-188
+      ndy = -(py - p.prev_xy[1]); pdx = px - p.prev_xy[0];                        // slam.cpp:190-196
+      predict_block3(pb, ndy, pdx, p.q_noise);
+    }
+    Cand best{INFINITY, 0x7fffffff};
+    for (int k = slice * (int)blockDim.x + threadIdx.x; k < cnt; k += P * (int)blockDim.x) {
+      const int a = 4 + 2 * k;
+      const double2 lm = *reinterpret_cast<const double2 *>(p.mu + a);
+      double4 pa = p.Pp[a], pbr = p.Pp[a + 1];
+      const double4 dk = p.D[k];
+      if (pred) {
+        pa.y = pa.x * ndy + pa.y; pa.z = pa.x * pdx + pa.z;
+        pbr.y = pbr.x * ndy + pbr.y; pbr.z = pbr.x * pdx + pbr.z;
+      }
+      const Lin L = linearize(th, px, py, lm.x, lm.y);
+      const double par3[3] = {pa.x, pa.y, pa.z}, pbr3[3] = {pbr.x, pbr.y, pbr.z};
+      const Block5 B = make_block5(pb, par3, pbr3, dk.x, dk.y, dk.z);
+      const Innov I = innovation(B, L, p.r_noise);
+      const double zd0 = z.r - L.zhat_r, zd1 = normalize_angle(z.phi - L.zhat_b);
+      double i00, i01, i11;
+      const double d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
+      best = cand_min(best, Cand{d, k});
+    }
+    best = warp_argmin(best);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      Cand c = s_red[0];
+      for (int w = 1; w < (int)blockDim.x / 32; ++w) c = cand_min(c, s_red[w]);
+      p.part_d[t * kGuessMaxSlices + slice] = c.d;
+      p.part_k[t * kGuessMaxSlices + slice] = c.k;
+      __threadfence();
+      const unsigned int prev = atomicAdd(p.ticket + t, 1u);
+      s_last = (prev == (unsigned int)(P - 1));
+      if (s_last) {
+        __threadfence();
+        p.ticket[t] = 0;                                     // ready for the next launch
+        Cand g{INFINITY, 0x7fffffff};
+        for (int q = 0; q < P; ++q)
+          g = cand_min(g, Cand{__ldcg(p.part_d + t * kGuessMaxSlices + q), __ldcg(p.part_k + t * kGuessMaxSlices + q)});
+        // generous acceptance (4 x threshold), as in shard_guess_kernel
+        int gj = (g.k < cnt && g.d <= 4.0 * p.thr) ? g.k : -1;
+        if (t == p.drop) gj = -1;
+        p.guess[t] = gj;
+        s_guess = gj;
+      }
+    }
+  }
+  __syncthreads();
+  if (!s_last || !p.push) return;
+  // ---- delivery of slot t by this CTA: the elements of the landmark's two raw columns that THIS rank stores ----
+  const int j = s_guess;
+  if (j >= 0 && j < p.N) {
+    const int a = 4 + 2 * j;
+    const bool own_a = ekf_lay_owns_row(p.lay, a);
+    for (int i = threadIdx.x; i < p.n_pad; i += blockDim.x) {
+      double2 v;
+      if (i > a + 1) {
+        if (!ekf_lay_owns_row(p.lay, i)) continue;
+        v = *reinterpret_cast<const double2 *>(p.sigma + ekf_lay_elem(p.lay, i, a));
+      } else if (i < a) {
+        if (!own_a) continue;
+        v.x = p.sigma[ekf_lay_elem(p.lay, a, i)];
+        v.y = p.sigma[ekf_lay_elem(p.lay, a + 1, i)];
+      } else {
+        continue;                          // the landmark's own 2 x 2 block comes from D
+      }
+      const int64_t e = (int64_t)t * p.n_pad + i;
+      for (int q = 0; q < p.peers.count; ++q) *reinterpret_cast<double2 *>(p.peers.cols[q] + e * 2) = v;
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_prev = atomicAdd(p.done_slots, 1u);
+  __syncthreads();
+  if (s_prev == gridDim.x - 1) {                             // the last of the m delivering CTAs
+    if (threadIdx.x == 0) *p.done_slots = 0;
+    __threadfence_system();
+    if ((int)threadIdx.x < p.peers.count) {
+      unsigned long long *dst = p.peers.flags[threadIdx.x] + p.peers.self;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(p.round_no) : "memory");
+    }
+  }
+}
+
 // ---- side state <-> Sigma -----------------------------------------------------------------------
 // side[0 .. 4 n_pad) = Pp rows (x, y, z, 0), side[4 n_pad ..) = D blocks (aa, ba, bb, 0): this rank's
 // owned rows, zero elsewhere (summed over the ranks afterwards)
