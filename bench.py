@@ -147,6 +147,15 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
+def _sm_clock(device_index):
+    try:
+        out = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm", "--format=csv,noheader,nounits", "-i",
+                              str(device_index)], capture_output=True, text=True, timeout=10).stdout.strip()
+        return float(out.splitlines()[0])
+    except Exception:
+        return None
+
+
 def make_workload(state0, count, m, n_scans, seed):
     """Per-scan poses and sightings for the large-map configs: the robot circles in the middle of the landmark
     grid; each scan sights the m nearest landmarks (body frame, sigma = 1e-3 per axis like nusim's fake sensor,
@@ -515,6 +524,15 @@ class MapRun:
         if self.world > 1:
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             dist.all_reduce(stored_all, op=dist.ReduceOp.SUM)
+        # per-rank view of the same loop (the sequential kernel of a rank also waits for the slowest rank's columns)
+        per_rank = None
+        if self.world > 1:
+            mine = {"seq_ms": float(np.mean(seq_ms)) if len(seq_ms) else None,
+                    "pass_ms": float(np.mean(dd_ms)) if len(dd_ms) else None,
+                    "sm_mhz": (clk or {}).get("sm_mhz") if self.rank == 0 else _sm_clock(local)}
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, mine)
+            per_rank = {k: [g[k] for g in gathered] for k in mine}
         b_scan, b_pass = algorithmic_bytes(self.n, m)
         peak, peak_src = peaks()
         dd_avg_ms = float(np.mean(dd_ms)) if len(dd_ms) else float("nan")
@@ -526,7 +544,7 @@ class MapRun:
         self.poses, self.xy, self.ids, self.next_scan = poses, xy, ids, W + 3 * K
         return {"value": value, "ms_per_step": ms_total / K, "e2e_value": K / (e2e_ms / 1000.0),
                 "e2e_ms_per_step": e2e_ms / K, "launches": int(launches), "assoc_ok": bool(ok.item()), "clocks": clk,
-                "overlap": bool(overlap),
+                "overlap": bool(overlap), "per_rank": per_rank,
                 "roofline": {"bound": "hbm", "kernel": "ekf_downdate_kernel", "achieved": achieved, "peak": peak,
                              "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                              "frac_nominal_8tbs": achieved / NOMINAL_HBM_GBS,
@@ -733,7 +751,7 @@ def run_ours(args):
                             "side of scan s+1 (ekf_set_overlap); the timed region ends after the last pass")
                            if res["overlap"] else "off (pass and sequential phase back to back on one stream)",
                 "association_bit_exact_vs_expected_ids": res["assoc_ok"],
-                "stored_triangle_gb": stored_gb},
+                "stored_triangle_gb": stored_gb, "per_rank": res["per_rank"]},
         "clocks": res["clocks"],
         "e2e": {"value": res["e2e_value"], "unit": UNIT, "h2d_bytes_per_step": 24 + 16 * m, "d2h_bytes_per_step": 32 + 4 * m,
                 "ms_per_step": res["e2e_ms_per_step"]},

@@ -34,6 +34,12 @@ struct ekf_filter {
   bool side_valid = false; // sharded: Pp / D replicated and current
   bool side_dirty = false; // sharded: Pp / D are NEWER than the Sigma entries they mirror (written back lazily)
   const double *pend_pose = nullptr;   // the round opened by ekf_shard_scan_begin predicts from this pose (or nullptr)
+  // shard protocol: the covariance pass of a round runs on its own stream, so that what the caller enqueues next on
+  // the handle's stream (input copies, the next round's speculative association) is ordered after the SEQUENTIAL
+  // kernel only and runs behind the pass; everything that touches Sigma or the panels waits for shard_ev_pass
+  cudaStream_t shard_stream = nullptr;
+  cudaEvent_t shard_ev_seq = nullptr, shard_ev_pass = nullptr;
+  bool shard_pass_pending = false;
   double *cols = nullptr;  // sharded: exchange buffer, kMaxChunkM x n_pad x 2
   int *guess = nullptr;    // sharded: speculative association of the round
   int *done_dev = nullptr; // sharded: measurements processed by the last finish

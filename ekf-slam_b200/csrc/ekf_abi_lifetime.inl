@@ -70,6 +70,11 @@ int ekf_destroy(ekf_filter *f) {
   {
     DeviceGuard guard(f->device);
     if (f->stream) cudaStreamSynchronize(f->stream);
+    if (f->shard_stream) {
+      cudaStreamSynchronize(f->shard_stream);
+      cudaStreamDestroy(f->shard_stream);
+      cudaEventDestroy(f->shard_ev_seq); cudaEventDestroy(f->shard_ev_pass);
+    }
     pipe_release(f);
     cudaFree(f->sigma); cudaFree(f->mu); cudaFree(f->W); cudaFree(f->V);
     cudaFree(f->Pp); cudaFree(f->cnt); cudaFree(f->status);   // D lives in the Pp allocation
@@ -247,6 +252,7 @@ int ekf_synchronize(ekf_filter *f) {
   if (!f) return EKF_ERR_INVALID;
   DeviceGuard guard(f->device);
   if (f->back_stream) CK(f, cudaStreamSynchronize(f->back_stream));   // a pass of the overlapped mode (no drain)
+  if (f->shard_stream) CK(f, cudaStreamSynchronize(f->shard_stream));  // a pass of the shard protocol
   CK(f, cudaStreamSynchronize(f->stream));
   return EKF_OK;
 }
@@ -271,6 +277,7 @@ int ekf_enable_timing(ekf_filter *f, int32_t ring_scans) {
   DeviceGuard guard(f->device);
   CK(f, cudaStreamSynchronize(f->stream));
   if (f->back_stream) CK(f, cudaStreamSynchronize(f->back_stream));
+  if (f->shard_stream) CK(f, cudaStreamSynchronize(f->shard_stream));
   for (auto &e : f->ev) if (e) cudaEventDestroy(e);
   f->ev.assign((size_t)ring_scans * 4, nullptr);   // sequential start / end, pass start / end
   for (auto &e : f->ev) CK(f, cudaEventCreate(&e));
@@ -284,6 +291,7 @@ int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t ma
   DeviceGuard guard(f->device);
   CK(f, cudaStreamSynchronize(f->stream));
   if (f->back_stream) CK(f, cudaStreamSynchronize(f->back_stream));
+  if (f->shard_stream) CK(f, cudaStreamSynchronize(f->shard_stream));
   int64_t have = f->ev_count < f->ev_cap ? f->ev_count : f->ev_cap;
   if (have > max_scans) have = max_scans;
   // the most recent `have` scans, oldest first

@@ -25,6 +25,15 @@ int shard_buffers(ekf_filter *f) {
   if (!f->cols) CK(f, cudaMalloc(&f->cols, (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double)));
   if (!f->guess) CK(f, cudaMalloc(&f->guess, kMaxChunkM * sizeof(int)));
   if (!f->done_dev) CK(f, cudaMalloc(&f->done_dev, sizeof(int)));
+  if (!f->shard_stream) {
+    CK(f, cudaStreamCreateWithFlags(&f->shard_stream, cudaStreamNonBlocking));
+    CK(f, cudaEventCreateWithFlags(&f->shard_ev_seq, cudaEventDisableTiming));
+    CK(f, cudaEventCreateWithFlags(&f->shard_ev_pass, cudaEventDisableTiming));
+    // the speculative association runs beside the covariance pass of the previous round: an SM changes its L1 /
+    // shared-memory split only when idle, so it asks for the pass's carve-out
+    CK(f, cudaFuncSetAttribute(shard_begin_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                               cudaSharedmemCarveoutMaxShared));
+  }
   if (!f->guess_part_d) {
     CK(f, cudaMalloc(&f->guess_part_d, (size_t)kMaxChunkM * kGuessMaxSlices * sizeof(double)));
     CK(f, cudaMalloc(&f->guess_part_k, (size_t)kMaxChunkM * kGuessMaxSlices * sizeof(int)));
@@ -36,6 +45,12 @@ int shard_buffers(ekf_filter *f) {
 
 // Back to the single-buffer state every other entry point expects.  Cheap when nothing is in flight.
 int pipe_drain(ekf_filter *f, bool keep_side = false) {
+  // a covariance pass of the shard protocol still running on its own stream: order the handle's stream after it
+  // (keep_side: the next shard round, which waits for it itself - after its speculative association)
+  if (f->shard_pass_pending && !keep_side) {
+    CK(f, cudaStreamWaitEvent(f->stream, f->shard_ev_pass, 0));
+    f->shard_pass_pending = false;
+  }
   // the shard protocol keeps the pose panel / diagonal blocks current in Pp / D only; everything that reads or
   // rewrites Sigma gets them written back first (keep_side: the next shard round, which does not read them there)
   if (f->side_dirty && !keep_side && !f->pipe_active) {

@@ -107,8 +107,17 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
   if (slices > kGuessMaxSlices) slices = kGuessMaxSlices;
   if (slices < 1) slices = 1;
   f->pend_peer = shard_peer_mode(f) ? 1 : 0;
-  // ONE kernel: the prediction is applied on the fly (the sequential kernel applies it to the replicated Pp when it
-  // starts), the last CTA of every sighting delivers its landmark's columns to every rank (peer mode)
+  { const int rcb = shard_buffers(f); if (rcb != EKF_OK) return rcb; }
+  // The previous round's covariance pass runs on the shard stream; what the caller enqueued on the handle's stream
+  // since (the input copies of this scan) ran behind it.  The kernels of this round do not: measured (2 GPUs,
+  // N = 10,000) a speculative association co-resident with the pass slows the pass by a third - its CTAs take the
+  // registers the pass's CTA needs on the same SM - for 16 us of hidden work.
+  if (f->shard_pass_pending) {
+    CK(f, cudaStreamWaitEvent(f->stream, f->shard_ev_pass, 0));
+    f->shard_pass_pending = false;
+  }
+  // (1) speculative association, prediction applied on the fly (the sequential kernel applies it to the replicated Pp
+  //     when it starts)
   BeginParams bp{};
   bp.Pp = f->Pp; bp.D = f->D; bp.mu = f->mu; bp.cnt = f->cnt;
   bp.pose = pose_dev; bp.prev_xy = f->prev_xy;
@@ -117,25 +126,26 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
   bp.part_d = f->guess_part_d; bp.part_k = f->guess_part_k; bp.ticket = f->guess_ticket;
   bp.drop = env_int("EKF_SHARD_DROP_GUESS", -1);       // test-only fault injection (stop / resume path)
   if (bp.drop >= mc) bp.drop = -1;
-  bp.push = f->pend_peer;
-  bp.sigma = f->sigma; bp.lay = f->lay; bp.n_pad = f->n_pad; bp.N = f->N;
-  if (f->pend_peer) {
-    f->xchg_round++;
-    bp.peers.count = f->cfg.shard_count; bp.peers.self = f->cfg.shard_rank;
-    const size_t par_off = (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes;
-    for (int q = 0; q < bp.peers.count; ++q) {
-      bp.peers.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
-      bp.peers.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
-    }
-    bp.round_no = f->xchg_round; bp.done_slots = f->push_done;
-  }
   shard_begin_kernel<<<dim3(mc, slices), kGuessThreads, 0, f->stream>>>(bp);
   f->launches++;
-  if (!f->pend_peer) {
-    shard_extract_cols_kernel<<<f->num_sms * 4, 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad, f->N, f->guess, mc,
-                                                                     f->cols);
-    f->launches++;
+  // (2) the columns, from Sigma as the previous round's pass left it
+  if (f->pend_peer) {
+    // extraction + delivery + arrival flags in one kernel over peer memory: nothing left for the caller
+    f->xchg_round++;
+    PeerTable pt{};
+    pt.count = f->cfg.shard_count; pt.self = f->cfg.shard_rank;
+    const size_t par_off = (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes;
+    for (int q = 0; q < pt.count; ++q) {
+      pt.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
+      pt.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
+    }
+    shard_push_cols_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->stream>>>(
+        f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt, f->xchg_round, f->push_done);
+  } else {
+    shard_extract_cols_kernel<<<dim3((f->n_pad + 255) / 256, mc), 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad,
+                                                                                    f->N, f->guess, mc, f->cols);
   }
+  f->launches++;
   CK(f, cudaGetLastError());
   f->pend_pose = pose_dev;
   f->pend_m = mc; f->pend_xy = xy_dev; f->pend_ids = ids_dev;
@@ -197,11 +207,22 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
                                     seq_smem_bytes(f->seq_threads, hot), f->stream));
   f->launches++;
-  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 1], f->stream)); CK(f, cudaEventRecord(f->ev[slot + 2], f->stream)); }
+  if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
   // association / done / pose / count are final here: hand them to the host before the covariance pass
   if (results_bytes > 0)
     CK(f, cudaMemcpyAsync(results_host, results_dev, (size_t)results_bytes, cudaMemcpyDeviceToHost, f->stream));
   if (results_event) CK(f, cudaEventRecord((cudaEvent_t)results_event, f->stream));
+  // A caller that takes the results early (results_event / results_host: the host-buffer loop) gets the covariance
+  // pass on the shard stream, ordered after the sequential kernel: what it enqueues next on the handle's stream (the
+  // next scan's input copies) then runs behind the pass.  A device-resident pipeline keeps everything on one stream:
+  // the two cross-stream hops cost it ~10 us per scan and hide nothing.
+  const bool side = (results_event != nullptr || results_bytes > 0) && env_int("EKF_SHARD_SIDE_PASS", 1) != 0;
+  cudaStream_t pass_stream = f->stream;
+  if (side) {
+    CK(f, cudaEventRecord(f->shard_ev_seq, f->stream));
+    CK(f, cudaStreamWaitEvent(f->shard_stream, f->shard_ev_seq, 0));
+    pass_stream = f->shard_stream;
+  }
   DdParams dp{};
   dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
   dp.n_pad = f->n_pad; dp.kmax = f->kmax; dp.k2 = (2 * mc + 3) & ~3;
@@ -210,13 +231,18 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   dp.total_chunks = dd_total_chunks(64, dp.row_begin, dp.row_end);   // shard bounds are multiples of 128 rows
   long long grid = f->dd_grid;
   if (grid > dp.total_chunks) grid = dp.total_chunks;
-  ekf_downdate_kernel<64, 2><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), f->stream>>>(dp);
+  if (timed) CK(f, cudaEventRecord(f->ev[slot + 2], pass_stream));
+  ekf_downdate_kernel<64, 2><<<(unsigned)grid, dd_threads(64), dd_smem_bytes(64, dp.k2), pass_stream>>>(dp);
   // Pp / D now hold the current pose panel / diagonal blocks; the Sigma entries they mirror (which the pass has
   // just recomputed with its own rounding) are written back lazily, by whatever reads or rewrites Sigma next
   f->side_dirty = true;
   f->launches += 1;
   CK(f, cudaGetLastError());
-  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 3], f->stream)); f->ev_count++; }
+  if (timed) { CK(f, cudaEventRecord(f->ev[slot + 3], pass_stream)); f->ev_count++; }
+  if (side) {
+    CK(f, cudaEventRecord(f->shard_ev_pass, f->shard_stream));
+    f->shard_pass_pending = true;
+  }
   return EKF_OK;
 }
 

@@ -147,24 +147,24 @@ __global__ void __launch_bounds__(kGuessThreads) shard_guess_kernel(const double
 // block; every element is written by every rank (zero unless owned).
 __global__ void shard_extract_cols_kernel(const double *sigma, EkfLay lay, int n_pad, int N, const int *guess,
                                           int m, double *cols) {
-  const int64_t total = (int64_t)m * n_pad;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    const int slot = (int)(e / n_pad), i = (int)(e % n_pad);
-    const int j = guess[slot];
-    double2 v = make_double2(0.0, 0.0);
-    if (j >= 0 && j < N) {
-      const int a = 4 + 2 * j;
-      if (i > a + 1) {
-        if (ekf_lay_owns_row(lay, i)) v = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a));
-      } else if (i < a) {
-        if (ekf_lay_owns_row(lay, a)) {
-          v.x = sigma[ekf_lay_elem(lay, a, i)];
-          v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
-        }
+  // grid = (ceil(n_pad / blockDim), m), one thread per (slot, row)
+  const int slot = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pad || slot >= m) return;
+  const int j = guess[slot];
+  double2 v = make_double2(0.0, 0.0);
+  if (j >= 0 && j < N) {
+    const int a = 4 + 2 * j;
+    if (i > a + 1) {
+      if (ekf_lay_owns_row(lay, i)) v = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a));
+    } else if (i < a) {
+      if (ekf_lay_owns_row(lay, a)) {
+        v.x = sigma[ekf_lay_elem(lay, a, i)];
+        v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
       }
     }
-    *reinterpret_cast<double2 *>(cols + e * 2) = v;
   }
+  *reinterpret_cast<double2 *>(cols + ((int64_t)slot * n_pad + i) * 2) = v;
 }
 
 // ---- overlapped scans on one GPU (ekf_set_overlap): the columns of the covariance the PENDING pass will produce ---
@@ -217,31 +217,52 @@ struct PeerTable {
   double *cols[kMaxPeers];                 // this round's column buffer of every rank
   unsigned long long *flags[kMaxPeers];    // flag array of every rank: flags[q][g] = rounds rank g has pushed to q
 };
-__global__ void shard_push_cols_kernel(const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m,
-                                       PeerTable peers, unsigned long long round_no, unsigned int *done_ctas) {
-  const int64_t total = (int64_t)m * n_pad;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-    const int slot = (int)(e / n_pad), i = (int)(e % n_pad);
-    const int j = guess[slot];
-    if (j < 0 || j >= N) continue;
-    const int a = 4 + 2 * j;
-    double2 v;
-    if (i > a + 1) {
-      if (!ekf_lay_owns_row(lay, i)) continue;
-      v = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a));
-    } else if (i < a) {
-      if (!ekf_lay_owns_row(lay, a)) continue;
-      v.x = sigma[ekf_lay_elem(lay, a, i)];
-      v.y = sigma[ekf_lay_elem(lay, a + 1, i)];
-    } else {
-      continue;                            // the landmark's own 2 x 2 block comes from D, not from here
+// One thread per ROW, all m slots: a thread first gathers its (up to 8 at a time) owned elements, then stores them to
+// every rank - the loads of a batch are in flight together (the compiler cannot hoist them over the peer stores
+// itself: the pointers may alias).  One arrival ticket per CTA: with a thread per (slot, row) the 1,580 same-address
+// atomics of the tickets alone took ~10 us (profiles/r2h_shard_launches_R8.csv).
+constexpr int kPushThreads = 128;
+__global__ void __launch_bounds__(kPushThreads) shard_push_cols_kernel(
+    const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m, PeerTable peers,
+    unsigned long long round_no, unsigned int *done_ctas) {
+  __shared__ int s_guess[32];
+  __shared__ unsigned int s_prev;
+  if (threadIdx.x < 32) s_guess[threadIdx.x] = (int)threadIdx.x < m ? guess[threadIdx.x] : -1;
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool own_i = i < n_pad && ekf_lay_owns_row(lay, i);
+  bool any = false;
+  for (int s0 = 0; s0 < m; s0 += 8) {
+    double2 v[8];
+    bool st[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      st[u] = false;
+      const int slot = s0 + u;
+      const int j = slot < m ? s_guess[slot] : -1;
+      if (j < 0 || j >= N || i >= n_pad) continue;
+      const int a = 4 + 2 * j;
+      if (i > a + 1) {
+        if (own_i) { v[u] = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a)); st[u] = true; }
+      } else if (i < a) {
+        if (ekf_lay_owns_row(lay, a)) {
+          v[u].x = sigma[ekf_lay_elem(lay, a, i)];
+          v[u].y = sigma[ekf_lay_elem(lay, a + 1, i)];
+          st[u] = true;
+        }
+      }                                    // (the landmark's own 2 x 2 block comes from D, not from here)
     }
-    for (int q = 0; q < peers.count; ++q) *reinterpret_cast<double2 *>(peers.cols[q] + e * 2) = v;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (!st[u]) continue;
+      any = true;
+      const int64_t e = (int64_t)(s0 + u) * n_pad + i;
+      for (int q = 0; q < peers.count; ++q) *reinterpret_cast<double2 *>(peers.cols[q] + e * 2) = v[u];
+    }
   }
   // arrival: every CTA's stores are visible system-wide before the flags move
-  __threadfence_system();
+  if (__syncthreads_or(any ? 1 : 0)) __threadfence_system();
   __syncthreads();
-  __shared__ unsigned int s_prev;
   if (threadIdx.x == 0) s_prev = atomicAdd(done_ctas, 1u);
   __syncthreads();
   if (s_prev == gridDim.x - 1) {
@@ -269,15 +290,16 @@ __global__ void shard_wait_peers_kernel(const unsigned long long *flags, int cou
   atomicMax(status, kErrPeerTimeout);
 }
 
-// ---- the whole begin phase as ONE kernel (peer mode): prediction on the fly + speculative association + delivery ----
-// Replaces shard_predict_kernel + shard_guess_kernel + shard_push_cols_kernel (three launches, ~0.05 ms of launch
-// gaps and ramps at 8 GPUs) on the per-scan path:
-//   * the prediction is not applied here at all: every candidate's pose-panel rows and the pose block are
-//     transformed in registers (slam.cpp:194-198 restricted to the n x 3 panel) - the sequential kernel applies
-//     the same transform to the replicated Pp when it starts (SeqParams::do_predict with side_mode);
-//   * the last CTA of a sighting to finish (ticket) reduces the slices' candidates to guess[t] and then DELIVERS:
-//     it stores the part this rank owns of the raw Sigma_0 columns of that landmark into every rank's buffer;
-//   * the last of those m delivering CTAs raises this rank's arrival flag everywhere (system-scope release).
+// ---- begin phase of the per-scan path: prediction on the fly + speculative association -------------------------
+// Replaces shard_predict_kernel + shard_guess_kernel on the sharded path:
+//   * the prediction is not applied here at all: the candidates' pose-panel rows and the pose block are transformed
+//     in registers (slam.cpp:194-198 restricted to the n x 3 panel) - the sequential kernel applies the same
+//     transform to the replicated Pp when it starts (SeqParams::do_predict with side_mode);
+//   * every slice is reduced to its landmark nearest to the sighting and only that one gets a Mahalanobis distance;
+//     the last CTA of a sighting to finish (ticket) reduces the slices' candidates to guess[t].
+// Delivery of the columns stays a separate, fully parallel kernel (shard_push_cols_kernel / shard_extract_cols_kernel):
+// fused into the last CTA of each sighting it was one CTA walking 20,096 rows with dependent gathers - 23-36 us
+// instead of 5 (profiles/r2g_shard_launches_*.csv).
 struct BeginParams {
   const double4 *Pp, *D;
   const double *mu;
@@ -292,13 +314,6 @@ struct BeginParams {
   int *part_k;
   unsigned int *ticket;
   int drop;                  // test-only fault injection: forget the speculation of this sighting (-1 = none)
-  int push;                  // 1: deliver through peer memory here; 0: the caller extracts and all-reduces
-  const double *sigma;
-  EkfLay lay;
-  int n_pad, N;
-  PeerTable peers;
-  unsigned long long round_no;
-  unsigned int *done_slots;
 };
 
 // A P A^T + Qbar on the 3 x 3 pose block, lower triangle rules (the arithmetic of shard_predict_kernel / phase 0 of
@@ -331,12 +346,10 @@ __device__ __forceinline__ void predict_block3(double P[3][3], double ndy, doubl
 
 __global__ void __launch_bounds__(kGuessThreads) shard_begin_kernel(const BeginParams p) {
   __shared__ Cand s_red[kGuessThreads / 32];
-  __shared__ int s_last, s_guess;
-  __shared__ unsigned int s_prev;
+  __shared__ int s_last;
   const int t = blockIdx.x, slice = blockIdx.y, P = gridDim.y;
   if (p.ids != nullptr) {                                  // known association: nothing to speculate
-    if (slice != 0) return;
-    if (threadIdx.x == 0) { s_guess = p.ids[t]; p.guess[t] = s_guess; s_last = 1; }
+    if (slice == 0 && threadIdx.x == 0) p.guess[t] = p.ids[t];
   } else {
     const int cnt = *p.cnt;
     const Polar z = to_polar(p.xy[2 * t], p.xy[2 * t + 1]);
@@ -353,24 +366,17 @@ __global__ void __launch_bounds__(kGuessThreads) shard_begin_kernel(const BeginP
       ndy = -(py - p.prev_xy[1]); pdx = px - p.prev_xy[0];                        // slam.cpp:190-196
       predict_block3(pb, ndy, pdx, p.q_noise);
     }
+    // This is a SPECULATION (it only decides which columns travel; the sequential kernel re-derives every association
+    // exactly and stops if it ever needs a landmark that was not fetched), so the slice is first reduced to its
+    // candidate NEAREST to the sighting's world position (two loads and three flops per landmark instead of the ~400
+    // instructions of a Mahalanobis distance), and only that one is evaluated in full.  The landmark with the smallest
+    // Mahalanobis distance is the nearest one unless the uncertainties of neighbouring landmarks differ wildly.
+    const double wx = px + z.r * cos(z.phi + th), wy = py + z.r * sin(z.phi + th);
     Cand best{INFINITY, 0x7fffffff};
     for (int k = slice * (int)blockDim.x + threadIdx.x; k < cnt; k += P * (int)blockDim.x) {
-      const int a = 4 + 2 * k;
-      const double2 lm = *reinterpret_cast<const double2 *>(p.mu + a);
-      double4 pa = p.Pp[a], pbr = p.Pp[a + 1];
-      const double4 dk = p.D[k];
-      if (pred) {
-        pa.y = pa.x * ndy + pa.y; pa.z = pa.x * pdx + pa.z;
-        pbr.y = pbr.x * ndy + pbr.y; pbr.z = pbr.x * pdx + pbr.z;
-      }
-      const Lin L = linearize(th, px, py, lm.x, lm.y);
-      const double par3[3] = {pa.x, pa.y, pa.z}, pbr3[3] = {pbr.x, pbr.y, pbr.z};
-      const Block5 B = make_block5(pb, par3, pbr3, dk.x, dk.y, dk.z);
-      const Innov I = innovation(B, L, p.r_noise);
-      const double zd0 = z.r - L.zhat_r, zd1 = normalize_angle(z.phi - L.zhat_b);
-      double i00, i01, i11;
-      const double d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
-      best = cand_min(best, Cand{d, k});
+      const double2 lm = *reinterpret_cast<const double2 *>(p.mu + 4 + 2 * k);
+      const double ex = lm.x - wx, ey = lm.y - wy;
+      best = cand_min(best, Cand{ex * ex + ey * ey, k});
     }
     best = warp_argmin(best);
     if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = best;
@@ -378,6 +384,24 @@ __global__ void __launch_bounds__(kGuessThreads) shard_begin_kernel(const BeginP
     if (threadIdx.x == 0) {
       Cand c = s_red[0];
       for (int w = 1; w < (int)blockDim.x / 32; ++w) c = cand_min(c, s_red[w]);
+      if (c.k < cnt) {                                     // the slice's nearest landmark, in full: slam.cpp:364-404
+        const int k = c.k, a = 4 + 2 * k;
+        const double2 lm = *reinterpret_cast<const double2 *>(p.mu + a);
+        double4 pa = p.Pp[a], pbr = p.Pp[a + 1];
+        const double4 dk = p.D[k];
+        if (pred) {
+          pa.y = pa.x * ndy + pa.y; pa.z = pa.x * pdx + pa.z;
+          pbr.y = pbr.x * ndy + pbr.y; pbr.z = pbr.x * pdx + pbr.z;
+        }
+        const Lin L = linearize(th, px, py, lm.x, lm.y);
+        const double par3[3] = {pa.x, pa.y, pa.z}, pbr3[3] = {pbr.x, pbr.y, pbr.z};
+        const Block5 B = make_block5(pb, par3, pbr3, dk.x, dk.y, dk.z);
+        const Innov I = innovation(B, L, p.r_noise);
+        const double zd0 = z.r - L.zhat_r, zd1 = normalize_angle(z.phi - L.zhat_b);
+        double i00, i01, i11;
+        c.d = mahalanobis(I.s00, I.s01, I.s11, zd0, zd1, i00, i01, i11);
+        if (!(c.d < INFINITY)) c = Cand{INFINITY, 0x7fffffff};
+      }
       p.part_d[t * kGuessMaxSlices + slice] = c.d;
       p.part_k[t * kGuessMaxSlices + slice] = c.k;
       __threadfence();
@@ -393,43 +417,7 @@ __global__ void __launch_bounds__(kGuessThreads) shard_begin_kernel(const BeginP
         int gj = (g.k < cnt && g.d <= 4.0 * p.thr) ? g.k : -1;
         if (t == p.drop) gj = -1;
         p.guess[t] = gj;
-        s_guess = gj;
       }
-    }
-  }
-  __syncthreads();
-  if (!s_last || !p.push) return;
-  // ---- delivery of slot t by this CTA: the elements of the landmark's two raw columns that THIS rank stores ----
-  const int j = s_guess;
-  if (j >= 0 && j < p.N) {
-    const int a = 4 + 2 * j;
-    const bool own_a = ekf_lay_owns_row(p.lay, a);
-    for (int i = threadIdx.x; i < p.n_pad; i += blockDim.x) {
-      double2 v;
-      if (i > a + 1) {
-        if (!ekf_lay_owns_row(p.lay, i)) continue;
-        v = *reinterpret_cast<const double2 *>(p.sigma + ekf_lay_elem(p.lay, i, a));
-      } else if (i < a) {
-        if (!own_a) continue;
-        v.x = p.sigma[ekf_lay_elem(p.lay, a, i)];
-        v.y = p.sigma[ekf_lay_elem(p.lay, a + 1, i)];
-      } else {
-        continue;                          // the landmark's own 2 x 2 block comes from D
-      }
-      const int64_t e = (int64_t)t * p.n_pad + i;
-      for (int q = 0; q < p.peers.count; ++q) *reinterpret_cast<double2 *>(p.peers.cols[q] + e * 2) = v;
-    }
-  }
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) s_prev = atomicAdd(p.done_slots, 1u);
-  __syncthreads();
-  if (s_prev == gridDim.x - 1) {                             // the last of the m delivering CTAs
-    if (threadIdx.x == 0) *p.done_slots = 0;
-    __threadfence_system();
-    if ((int)threadIdx.x < p.peers.count) {
-      unsigned long long *dst = p.peers.flags[threadIdx.x] + p.peers.self;
-      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(p.round_no) : "memory");
     }
   }
 }
