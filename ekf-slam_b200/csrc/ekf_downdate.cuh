@@ -10,8 +10,9 @@
 // Roofline: 16 B of HBM traffic and 4m fp64 flop per stored entry.  At m = 20 that is 3.2 GB and
 // 16.3 GFLOP per pass at N = 10,000: 0.49 ms at the measured 6.5 TB/s against 0.44 ms at the
 // fp64 peak (37 TFLOP/s), so BOTH limits bind and neither the FMA issue slots nor the shared-memory
-// operand traffic of a scalar DFMA loop can be afforded (round-1 profile, profiles/r3_*: the
-// DFMA version ran at 58 % fp64-pipe and 72 % shared-memory wavefront utilisation, 0.78 ms).
+// operand traffic of a scalar DFMA loop can be afforded (first version of round 1, ncu capture in
+// profiles/earlier/r1_downdate_ncu_full_summary.csv: the DFMA loop ran at 58 % fp64-pipe and 72 %
+// shared-memory wavefront utilisation, 0.78 ms).
 // Structure of this version:
 //   * persistent CTAs (one per SM), each walks a contiguous range of 64-row x 128-column chunks
 //     of the column strips (ekf_layout.h); a chunk is one contiguous 64 KiB byte range;
@@ -20,7 +21,7 @@
 //     8 conflict-free LDS.64 fragment loads for 16 DMMAs (the DFMA loop needed 6 LDS.128 per
 //     32 DFMA per thread);
 //   * Sigma goes HBM -> registers -> HBM directly in accumulator-fragment order with 256-bit
-//     accesses (LDG.E.256 / STG.E.256): the row/column interleave of ekf_panel_slot() makes every
+//     accesses (SASS LDG.E.NA.ENL2.256 / STG.E.ENL2.256, profiles/sass_excerpt.txt): the row/column interleave of ekf_panel_slot() makes every
 //     thread own 4 contiguous doubles, every warp access 8 full 128-byte lines; the next chunk's
 //     tile is prefetched into a second register set while the current one is updated;
 //   * the strip's W rows (128 x 2m) stay resident in shared memory for the whole strip walk, double
