@@ -100,6 +100,7 @@ def load() -> C.CDLL:
         "ekf_set_sigma_block": (C.c_int, [vp, i32, i32, i32, i32, dp]),
         "ekf_fill_procedural": (C.c_int, [vp, C.c_uint64, i32, i32]),
         "ekf_mahalanobis": (C.c_int, [vp, C.c_double, C.c_double, dp, i32, C.POINTER(i32)]),
+        "ekf_mahalanobis_noalloc": (C.c_int, [vp, C.c_double, C.c_double, dp, i32, C.POINTER(i32)]),
         "ekf_sigma_storage": (C.c_int, [vp, i64p, i64p]),
         "ekf_launch_count": (C.c_int, [vp, i64p]),
         "ekf_read_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),

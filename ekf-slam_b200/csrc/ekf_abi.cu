@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -208,6 +209,7 @@ int env_int(const char *name, int dflt) {
 #include "ekf_abi_lifetime.inl"
 #include "ekf_abi_scan.inl"
 #include "ekf_abi_access.inl"
+#include "ekf_abi_noalloc.inl"
 #include "ekf_abi_batch.inl"
 #include "ekf_abi_shard.inl"
 #include "ekf_abi_landmarks.inl"

@@ -147,6 +147,17 @@ int ekf_set_sigma_block(ekf_filter *f, int32_t i0, int32_t i1, int32_t j0, int32
  * cap), against the filter as it stands; *count = counter_obstacles.  Read-only.  This is how tests and
  * bench.py log the decision margins (min |d - threshold|, best-vs-second gap) of a scan. */
 int ekf_mahalanobis(ekf_filter *f, double x, double y, double *out_d, int32_t cap, int32_t *count);
+/* The same sweep for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * ekf_mahalanobis stages the distances in a per-handle buffer that grows with cudaMalloc; this variant stages them in
+ * a file-scope static __device__ array of EKF_NOALLOC_MAX_LANDMARKS doubles (512 KiB, held by every GPU that loads the
+ * library until the process exits) and calls no cudaMalloc / cudaFree / allocating library routine.  Same kernel,
+ * bit-identical distances.  cap > EKF_NOALLOC_MAX_LANDMARKS is rejected with EKF_ERR_INVALID (ekf_last_cuda_error
+ * says why).  Every call on a GPU shares the one array, which keeps the last call's contents (nothing in it has to
+ * start at zero: a call reads back only what its own kernel wrote); calls that OVERLAP on one GPU - two handles on
+ * different streams, two host threads - race on it and must be serialised by the caller. */
+#define EKF_NOALLOC_MAX_LANDMARKS 65536
+int ekf_mahalanobis_noalloc(ekf_filter *f, double x, double y, double *out_d, int32_t cap, int32_t *count);
 /* Procedural large-map fixture: `count` landmarks on a jittered
  * unit grid of `grid_w` columns, state consistent with it, Sigma = block-diagonal SPD + a
  * rank-8 hash-generated cross term.  Deterministic in `seed`; generated on the device. */
