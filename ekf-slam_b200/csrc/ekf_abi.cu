@@ -53,6 +53,7 @@ struct ekf_filter {
   unsigned char *peer_base[16] = {};      // the same region of every rank (own entry = xchg), peer-mapped
   void *peer_ipc[16] = {};                // regions opened with cudaIpcOpenMemHandle (closed at destroy)
   int peers_attached = 0;
+  int peers_ipc = 0;                      // ... of which through a CUDA IPC handle (another process)
   unsigned long long xchg_round = 0;      // rounds pushed so far
   unsigned int *push_done = nullptr;      // last-CTA counter of the push kernel
   int pend_peer = 0;                      // the pending round was exchanged through peer memory

@@ -5,15 +5,16 @@ namespace {
 // the shard protocol also runs on an unsharded handle (one shard that owns every row)
 int shard_ok(ekf_filter *f) { return f != nullptr; }
 
-// the peer-visible exchange region: two column buffers (round parity) + the arrival flags
+// the peer-visible exchange region: two column buffers (round parity) + the arrival flags + the hop-1 flags
+constexpr size_t kXchgFlagBytes = 2 * kMaxPeers * sizeof(unsigned long long);
 int shard_xchg_region(ekf_filter *f) {
   if (f->xchg) return EKF_OK;
   f->xchg_cols_bytes = (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double);
-  const size_t total = 2 * f->xchg_cols_bytes + kMaxPeers * sizeof(unsigned long long);
+  const size_t total = 2 * f->xchg_cols_bytes + kXchgFlagBytes;
   CK(f, cudaMalloc(&f->xchg, total));
   CK(f, cudaMemset(f->xchg, 0, total));
-  CK(f, cudaMalloc(&f->push_done, sizeof(unsigned int)));
-  CK(f, cudaMemset(f->push_done, 0, sizeof(unsigned int)));
+  CK(f, cudaMalloc(&f->push_done, 2 * sizeof(unsigned int)));
+  CK(f, cudaMemset(f->push_done, 0, 2 * sizeof(unsigned int)));
   f->peer_base[f->cfg.shard_rank] = f->xchg;
   f->peers_attached = 1;
   return EKF_OK;
@@ -36,7 +37,7 @@ int ekf_shard_peer_export(ekf_filter *f, void *ipc_handle_64, void **local_base,
     memcpy(ipc_handle_64, &h, 64);
   }
   if (local_base) *local_base = f->xchg;
-  if (region_bytes) *region_bytes = (int64_t)(2 * f->xchg_cols_bytes + kMaxPeers * sizeof(unsigned long long));
+  if (region_bytes) *region_bytes = (int64_t)(2 * f->xchg_cols_bytes + kXchgFlagBytes);
   return EKF_OK;
 }
 
@@ -54,6 +55,7 @@ int ekf_shard_peer_attach(ekf_filter *f, int32_t peer_rank, const void *ipc_hand
     void *p = nullptr;
     CK(f, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     f->peer_ipc[peer_rank] = p;
+    f->peers_ipc++;
     f->peer_base[peer_rank] = static_cast<unsigned char *>(p);
   } else {
     f->peer_base[peer_rank] = static_cast<unsigned char *>(same_process_base);
@@ -139,8 +141,18 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
       pt.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
       pt.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
     }
-    shard_push_cols_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->stream>>>(
-        f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt, f->xchg_round, f->push_done);
+    // two-hop delivery when every peer is another process (its push kernel runs on its own stream whatever this rank
+    // does); handles of one process - which may share a stream - keep the direct kernel.  EKF_SHARD_TWO_HOP overrides.
+    const int two_hop = env_int("EKF_SHARD_TWO_HOP", (f->peers_ipc == pt.count - 1 && pt.count > 2) ? 1 : 0);
+    if (two_hop) {
+      PeerTable h1 = pt;
+      for (int q = 0; q < pt.count; ++q) h1.flags[q] = pt.flags[q] + kMaxPeers;
+      shard_push_cols_2hop_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->stream>>>(
+          f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt, h1, f->xchg_round, f->push_done, f->status);
+    } else {
+      shard_push_cols_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->stream>>>(
+          f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt, f->xchg_round, f->push_done);
+    }
   } else {
     shard_extract_cols_kernel<<<dim3((f->n_pad + 255) / 256, mc), 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad,
                                                                                     f->N, f->guess, mc, f->cols);

@@ -212,6 +212,7 @@ __global__ void pipe_extract_cols_kernel(const double *sigma, EkfLay lay, int n_
 // side is shard_wait_peers_kernel right before the sequential kernel.  Buffers alternate by round parity:
 // a fast rank may already push round r + 1 while a slow one still reads round r.
 constexpr int kMaxPeers = 16;
+constexpr int kErrPeerTimeout = 5;         // EKF_ERR_CUDA: the exchange did not complete
 struct PeerTable {
   int count, self;
   double *cols[kMaxPeers];                 // this round's column buffer of every rank
@@ -274,9 +275,131 @@ __global__ void __launch_bounds__(kPushThreads) shard_push_cols_kernel(
     }
   }
 }
+// ---- two-hop delivery (one process per GPU) ----------------------------------------------------------------------
+// In shard_push_cols_kernel the rank that stores row a of a sighted landmark ships the whole row segment (i < a) of
+// every slot to every peer: at 8 GPUs, N = 10,000, m = 20 that one rank stores ~22 MB over NVLink per scan while the
+// others ship a few hundred KB, and the other seven sequential kernels wait 30-40 us for it (bench.py run.per_rank).
+// Here the row segment travels in two hops, the way an all-gather balances its links: 128-row blocks are assigned to
+// RELAY ranks block-cyclically (block b -> rank b % R); hop 1: the owner stores block b's elements to itself and to
+// the relay only (3.2 MB out instead of 22); hop 2: the relay forwards what arrived to the remaining ranks (every rank
+// forwards ~1/R of the segment).  The column part (i > a + 1, stored by the rank that owns row i) is spread over the
+// ranks already and is delivered directly, as before.  One kernel: CTA b = row block b; after hop 1 the rank raises
+// its hop-1 flag everywhere; the relay CTAs (b % R == self) wait for every rank's hop-1 flag of this round (bounded),
+// forward, and the last CTA raises the arrival flag the sequential kernel waits for.  Needs every rank's push kernel
+// to make progress independently (one stream per rank): handles of ONE process that share a stream keep the direct
+// kernel (ekf_abi_shard.inl).
+static_assert(kPushThreads == EKF_STRIP, "one CTA per 128-row block");
+__global__ void __launch_bounds__(kPushThreads) shard_push_cols_2hop_kernel(
+    const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m, PeerTable peers,
+    PeerTable hop1, unsigned long long round_no, unsigned int *tickets, int *status) {
+  __shared__ int s_guess[32], s_owner[32];
+  __shared__ unsigned int s_prev;
+  const int R = peers.count, self = peers.self;
+  if (threadIdx.x < 32) {
+    const int j = (int)threadIdx.x < m ? guess[threadIdx.x] : -1;
+    s_guess[threadIdx.x] = j;
+    int own = -1;
+    if (j >= 0 && j < N) {                                   // the rank that stores rows a, a + 1 of landmark j
+      const int a = 4 + 2 * j;
+      for (int g = 0; g < R; ++g)
+        if (a >= ekf_shard_bound(n_pad, g, R) && a < ekf_shard_bound(n_pad, g + 1, R)) own = g;
+    }
+    s_owner[threadIdx.x] = own;
+  }
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int relay = (int)(blockIdx.x % (unsigned)R);
+  const bool own_i = i < n_pad && ekf_lay_owns_row(lay, i);
+  bool any = false;
+  for (int s0 = 0; s0 < m; s0 += 8) {
+    double2 v[8];
+    int kind[8];                                             // 0 nothing, 1 column part (to all), 2 row segment (hop 1)
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      kind[u] = 0;
+      const int slot = s0 + u;
+      const int j = slot < m ? s_guess[slot] : -1;
+      if (j < 0 || j >= N || i >= n_pad) continue;
+      const int a = 4 + 2 * j;
+      if (i > a + 1) {
+        if (own_i) { v[u] = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a)); kind[u] = 1; }
+      } else if (i < a) {
+        if (s_owner[slot] == self) {
+          v[u].x = sigma[ekf_lay_elem(lay, a, i)];
+          v[u].y = sigma[ekf_lay_elem(lay, a + 1, i)];
+          kind[u] = 2;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (kind[u] == 0) continue;
+      any = true;
+      const int64_t e = ((int64_t)(s0 + u) * n_pad + i) * 2;
+      if (kind[u] == 1 || relay == self) {                   // direct: every rank (the owner relays this block itself)
+        for (int q = 0; q < R; ++q) *reinterpret_cast<double2 *>(peers.cols[q] + e) = v[u];
+      } else {                                               // hop 1: own copy + the relay's
+        *reinterpret_cast<double2 *>(peers.cols[self] + e) = v[u];
+        *reinterpret_cast<double2 *>(peers.cols[relay] + e) = v[u];
+      }
+    }
+  }
+  // hop-1 arrival: this rank's stores are visible system-wide before its hop-1 flag moves
+  if (__syncthreads_or(any ? 1 : 0)) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_prev = atomicAdd(tickets, 1u);
+  __syncthreads();
+  if (s_prev == gridDim.x - 1) {
+    if (threadIdx.x == 0) tickets[0] = 0;
+    __threadfence_system();
+    if ((int)threadIdx.x < R) {
+      unsigned long long *dst = hop1.flags[threadIdx.x] + self;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(round_no) : "memory");
+    }
+  }
+  // hop 2: the relay CTAs forward what the other owners left in this rank's buffer
+  bool fwd = false;
+  if (relay == self) {
+    if ((int)threadIdx.x < R) {
+      unsigned long long t0, now, f;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      for (;;) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(f) : "l"(hop1.flags[self] + threadIdx.x) : "memory");
+        if (f >= round_no) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 >= 10000000000ull) { atomicMax(status, kErrPeerTimeout); break; }
+      }
+    }
+    __syncthreads();
+    if (i < n_pad) {
+      for (int slot = 0; slot < m; ++slot) {
+        const int j = s_guess[slot], own = s_owner[slot];
+        if (j < 0 || j >= N || own < 0 || own == self) continue;
+        if (i >= 4 + 2 * j) continue;
+        const int64_t e = ((int64_t)slot * n_pad + i) * 2;
+        const double2 w = __ldcg(reinterpret_cast<const double2 *>(peers.cols[self] + e));
+        for (int q = 0; q < R; ++q)
+          if (q != self && q != own) *reinterpret_cast<double2 *>(peers.cols[q] + e) = w;
+        fwd = true;
+      }
+    }
+  }
+  if (__syncthreads_or(fwd ? 1 : 0)) __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_prev = atomicAdd(tickets + 1, 1u);
+  __syncthreads();
+  if (s_prev == gridDim.x - 1) {
+    if (threadIdx.x == 0) tickets[1] = 0;
+    __threadfence_system();
+    if ((int)threadIdx.x < R) {
+      unsigned long long *dst = peers.flags[threadIdx.x] + self;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(round_no) : "memory");
+    }
+  }
+}
+
 // consumer side: wait until every rank has pushed round `round_no` into this rank's buffer.  Bounded: a peer
 // that never arrives (crashed process) latches kErrPeerTimeout after ~10 s instead of hanging the GPU.
-constexpr int kErrPeerTimeout = 5;         // EKF_ERR_CUDA: the exchange did not complete
 __global__ void shard_wait_peers_kernel(const unsigned long long *flags, int count, unsigned long long round_no,
                                         int *status) {
   if ((int)threadIdx.x >= count) return;
