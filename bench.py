@@ -496,6 +496,7 @@ class MapRun:
             f.set_overlap(False)
         self.barrier()
         seq_ms, dd_ms = f.read_timing(K)
+        xa_ms, xp_ms = f.read_timing_shard(K) if self.sharded else (np.zeros(0), np.zeros(0))
         f.enable_timing(0)
         if overlap:
             f.set_overlap(True)
@@ -529,6 +530,8 @@ class MapRun:
         if self.world > 1:
             mine = {"seq_ms": float(np.mean(seq_ms)) if len(seq_ms) else None,
                     "pass_ms": float(np.mean(dd_ms)) if len(dd_ms) else None,
+                    "assoc_ms": float(np.mean(xa_ms)) if len(xa_ms) else None,
+                    "push_ms": float(np.mean(xp_ms)) if len(xp_ms) else None,
                     "sm_mhz": (clk or {}).get("sm_mhz") if self.rank == 0 else _sm_clock(local)}
             gathered = [None] * self.world
             dist.all_gather_object(gathered, mine)

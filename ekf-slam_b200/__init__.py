@@ -105,6 +105,7 @@ def load() -> C.CDLL:
         "ekf_launch_count": (C.c_int, [vp, i64p]),
         "ekf_read_timing": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),
         "ekf_enable_timing": (C.c_int, [vp, i32]),
+        "ekf_read_timing_shard": (C.c_int, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float), i32, ip]),
         "ekf_shard_info": (C.c_int, [vp, ip, ip, i64p]),
         "ekf_shard_sync_begin": (C.c_int, [vp, C.POINTER(vp), i64p]),
         "ekf_shard_sync_finish": (C.c_int, [vp]),
@@ -417,6 +418,16 @@ class EkfSlam:
 
     def enable_timing(self, ring_scans: int):
         self._check(self._L.ekf_enable_timing(self._h, int(ring_scans)), "ekf_enable_timing")
+
+    def read_timing_shard(self, max_scans: int):
+        """(assoc_ms[], push_ms[]) of the begin phase of the most recent row-sharded scans (synchronises)."""
+        a = np.zeros(max_scans, dtype=np.float32)
+        b = np.zeros(max_scans, dtype=np.float32)
+        n = C.c_int32(0)
+        fp = C.POINTER(C.c_float)
+        self._check(self._L.ekf_read_timing_shard(self._h, a.ctypes.data_as(fp), b.ctypes.data_as(fp), max_scans,
+                                                  C.byref(n)), "ekf_read_timing_shard")
+        return a[:n.value].astype(np.float64), b[:n.value].astype(np.float64)
 
     def read_timing(self, max_scans: int):
         """(seq_ms[], downdate_ms[]) of the most recent scans, oldest first (synchronises)."""

@@ -39,8 +39,9 @@ struct ekf_filter {
   // the handle's stream (input copies, the next round's speculative association) is ordered after the SEQUENTIAL
   // kernel only and runs behind the pass; everything that touches Sigma or the panels waits for shard_ev_pass
   cudaStream_t shard_stream = nullptr;
-  cudaEvent_t shard_ev_seq = nullptr, shard_ev_pass = nullptr;
+  cudaEvent_t shard_ev_seq = nullptr, shard_ev_pass = nullptr, shard_ev_push = nullptr;
   bool shard_pass_pending = false;
+  std::vector<cudaEvent_t> ev_x;   // timing ring of the shard begin phase: association start / end, push start / end
   double *cols = nullptr;  // sharded: exchange buffer, kMaxChunkM x n_pad x 2
   int *guess = nullptr;    // sharded: speculative association of the round
   int *done_dev = nullptr; // sharded: measurements processed by the last finish
@@ -53,7 +54,6 @@ struct ekf_filter {
   unsigned char *peer_base[16] = {};      // the same region of every rank (own entry = xchg), peer-mapped
   void *peer_ipc[16] = {};                // regions opened with cudaIpcOpenMemHandle (closed at destroy)
   int peers_attached = 0;
-  int peers_ipc = 0;                      // ... of which through a CUDA IPC handle (another process)
   unsigned long long xchg_round = 0;      // rounds pushed so far
   unsigned int *push_done = nullptr;      // last-CTA counter of the push kernel
   int pend_peer = 0;                      // the pending round was exchanged through peer memory

@@ -73,7 +73,7 @@ int ekf_destroy(ekf_filter *f) {
     if (f->shard_stream) {
       cudaStreamSynchronize(f->shard_stream);
       cudaStreamDestroy(f->shard_stream);
-      cudaEventDestroy(f->shard_ev_seq); cudaEventDestroy(f->shard_ev_pass);
+      cudaEventDestroy(f->shard_ev_seq); cudaEventDestroy(f->shard_ev_pass); cudaEventDestroy(f->shard_ev_push);
     }
     pipe_release(f);
     cudaFree(f->sigma); cudaFree(f->mu); cudaFree(f->W); cudaFree(f->V);
@@ -91,6 +91,8 @@ int ekf_destroy(ekf_filter *f) {
     if (f->res_event) cudaEventDestroy(f->res_event);
     for (auto &e : f->ev) if (e) cudaEventDestroy(e);
     f->ev.clear();
+    for (auto &e : f->ev_x) if (e) cudaEventDestroy(e);
+    f->ev_x.clear();
     if (f->own_stream) cudaStreamDestroy(f->own_stream);
   }
   delete f;
@@ -270,6 +272,25 @@ int ekf_last_status(ekf_filter *f) {
   return s;
 }
 
+int ekf_read_timing_shard(ekf_filter *f, float *assoc_ms, float *push_ms, int32_t max_scans, int32_t *n_scans) {
+  if (!f || max_scans < 0) return EKF_ERR_INVALID;
+  DeviceGuard guard(f->device);
+  CK(f, cudaStreamSynchronize(f->stream));
+  if (f->shard_stream) CK(f, cudaStreamSynchronize(f->shard_stream));
+  int64_t have = f->ev_count < f->ev_cap ? f->ev_count : f->ev_cap;
+  if (have > max_scans) have = max_scans;
+  for (int64_t i = 0; i < have; ++i) {
+    const size_t slot = (size_t)((f->ev_count - have + i) % f->ev_cap) * 4;
+    float a = 0.f, b = 0.f;
+    if (cudaEventElapsedTime(&a, f->ev_x[slot], f->ev_x[slot + 1]) != cudaSuccess) { cudaGetLastError(); a = 0.f; }
+    if (cudaEventElapsedTime(&b, f->ev_x[slot + 2], f->ev_x[slot + 3]) != cudaSuccess) { cudaGetLastError(); b = 0.f; }
+    if (assoc_ms) assoc_ms[i] = a;
+    if (push_ms) push_ms[i] = b;
+  }
+  if (n_scans) *n_scans = (int32_t)have;
+  return EKF_OK;
+}
+
 const char *ekf_last_cuda_error(ekf_filter *f) { return f ? f->cuda_err.c_str() : ""; }
 
 int ekf_enable_timing(ekf_filter *f, int32_t ring_scans) {
@@ -281,6 +302,9 @@ int ekf_enable_timing(ekf_filter *f, int32_t ring_scans) {
   for (auto &e : f->ev) if (e) cudaEventDestroy(e);
   f->ev.assign((size_t)ring_scans * 4, nullptr);   // sequential start / end, pass start / end
   for (auto &e : f->ev) CK(f, cudaEventCreate(&e));
+  for (auto &e : f->ev_x) if (e) cudaEventDestroy(e);
+  f->ev_x.assign((size_t)ring_scans * 4, nullptr);
+  for (auto &e : f->ev_x) CK(f, cudaEventCreate(&e));
   f->ev_cap = ring_scans;
   f->ev_count = 0;
   return EKF_OK;

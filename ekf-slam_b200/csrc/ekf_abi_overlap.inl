@@ -29,6 +29,7 @@ int shard_buffers(ekf_filter *f) {
     CK(f, cudaStreamCreateWithFlags(&f->shard_stream, cudaStreamNonBlocking));
     CK(f, cudaEventCreateWithFlags(&f->shard_ev_seq, cudaEventDisableTiming));
     CK(f, cudaEventCreateWithFlags(&f->shard_ev_pass, cudaEventDisableTiming));
+    CK(f, cudaEventCreateWithFlags(&f->shard_ev_push, cudaEventDisableTiming));
     // the speculative association runs beside the covariance pass of the previous round: an SM changes its L1 /
     // shared-memory split only when idle, so it asks for the pass's carve-out
     CK(f, cudaFuncSetAttribute(shard_begin_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,

@@ -5,15 +5,26 @@ namespace {
 // the shard protocol also runs on an unsharded handle (one shard that owns every row)
 int shard_ok(ekf_filter *f) { return f != nullptr; }
 
-// the peer-visible exchange region: two column buffers (round parity) + the arrival flags + the hop-1 flags
+// the peer-visible exchange region: two column buffers (round parity, poisoned with kColsSentinel) + per-rank
+// completion flags [kMaxPeers] + per-rank credits [kMaxPeers]
 constexpr size_t kXchgFlagBytes = 2 * kMaxPeers * sizeof(unsigned long long);
+
+__global__ void shard_poison_kernel(double *buf, int64_t doubles) {
+  const double v = __longlong_as_double((long long)kColsSentinel);
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < doubles; e += (int64_t)gridDim.x * blockDim.x)
+    buf[e] = v;
+}
 int shard_xchg_region(ekf_filter *f) {
   if (f->xchg) return EKF_OK;
   f->xchg_cols_bytes = (size_t)kMaxChunkM * f->n_pad * 2 * sizeof(double);
   const size_t total = 2 * f->xchg_cols_bytes + kXchgFlagBytes;
   CK(f, cudaMalloc(&f->xchg, total));
   CK(f, cudaMemset(f->xchg, 0, total));
-  CK(f, cudaMalloc(&f->push_done, 2 * sizeof(unsigned int)));
+  shard_poison_kernel<<<f->num_sms * 4, 256>>>(reinterpret_cast<double *>(f->xchg),
+                                               (int64_t)(2 * f->xchg_cols_bytes / sizeof(double)));
+  CK(f, cudaGetLastError());
+  CK(f, cudaDeviceSynchronize());           // poisoned before any peer can be told about the region
+  CK(f, cudaMalloc(&f->push_done, 2 * sizeof(unsigned int)));   // tickets: push kernel, recycle kernel
   CK(f, cudaMemset(f->push_done, 0, 2 * sizeof(unsigned int)));
   f->peer_base[f->cfg.shard_rank] = f->xchg;
   f->peers_attached = 1;
@@ -55,7 +66,6 @@ int ekf_shard_peer_attach(ekf_filter *f, int32_t peer_rank, const void *ipc_hand
     void *p = nullptr;
     CK(f, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     f->peer_ipc[peer_rank] = p;
-    f->peers_ipc++;
     f->peer_base[peer_rank] = static_cast<unsigned char *>(p);
   } else {
     f->peer_base[peer_rank] = static_cast<unsigned char *>(same_process_base);
@@ -128,8 +138,12 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
   bp.part_d = f->guess_part_d; bp.part_k = f->guess_part_k; bp.ticket = f->guess_ticket;
   bp.drop = env_int("EKF_SHARD_DROP_GUESS", -1);       // test-only fault injection (stop / resume path)
   if (bp.drop >= mc) bp.drop = -1;
+  const bool timed_x = f->ev_cap > 0;
+  const size_t xs = timed_x ? (size_t)(f->ev_count % f->ev_cap) * 4 : 0;
+  if (timed_x) CK(f, cudaEventRecord(f->ev_x[xs], f->stream));
   shard_begin_kernel<<<dim3(mc, slices), kGuessThreads, 0, f->stream>>>(bp);
   f->launches++;
+  if (timed_x) CK(f, cudaEventRecord(f->ev_x[xs + 1], f->stream));
   // (2) the columns, from Sigma as the previous round's pass left it
   if (f->pend_peer) {
     // extraction + delivery + arrival flags in one kernel over peer memory: nothing left for the caller
@@ -141,18 +155,17 @@ int ekf_shard_scan_begin(ekf_filter *f, const double *pose_dev, int32_t m, const
       pt.cols[q] = reinterpret_cast<double *>(f->peer_base[q] + par_off);
       pt.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
     }
-    // two-hop delivery when every peer is another process (its push kernel runs on its own stream whatever this rank
-    // does); handles of one process - which may share a stream - keep the direct kernel.  EKF_SHARD_TWO_HOP overrides.
-    const int two_hop = env_int("EKF_SHARD_TWO_HOP", (f->peers_ipc == pt.count - 1 && pt.count > 2) ? 1 : 0);
-    if (two_hop) {
-      PeerTable h1 = pt;
-      for (int q = 0; q < pt.count; ++q) h1.flags[q] = pt.flags[q] + kMaxPeers;
-      shard_push_cols_2hop_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->stream>>>(
-          f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt, h1, f->xchg_round, f->push_done, f->status);
-    } else {
-      shard_push_cols_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->stream>>>(
-          f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt, f->xchg_round, f->push_done);
-    }
+    // ... on the SHARD stream, ordered after the speculation: the sequential kernel (handle's stream) starts at once and
+    // polls the elements it needs as they land (flag-in-data), so the delivery hides behind its first measurements
+    CK(f, cudaEventRecord(f->shard_ev_seq, f->stream));
+    CK(f, cudaStreamWaitEvent(f->shard_stream, f->shard_ev_seq, 0));
+    if (timed_x) CK(f, cudaEventRecord(f->ev_x[xs + 2], f->shard_stream));
+    shard_push_cols_kernel<<<(f->n_pad + kPushThreads - 1) / kPushThreads, kPushThreads, 0, f->shard_stream>>>(
+        f->sigma, f->lay, f->n_pad, f->N, f->guess, mc, pt,
+        reinterpret_cast<const unsigned long long *>(f->xchg + 2 * f->xchg_cols_bytes) + kMaxPeers, f->xchg_round,
+        f->push_done, f->status, env_int("EKF_SHARD_TWO_HOP", pt.count > 2 ? 1 : 0));
+    if (timed_x) CK(f, cudaEventRecord(f->ev_x[xs + 3], f->shard_stream));
+    CK(f, cudaEventRecord(f->shard_ev_push, f->shard_stream));
   } else {
     shard_extract_cols_kernel<<<dim3((f->n_pad + 255) / 256, mc), 256, 0, f->stream>>>(f->sigma, f->lay, f->n_pad,
                                                                                     f->N, f->guess, mc, f->cols);
@@ -196,10 +209,8 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   if (f->pend_peer) {
     // every rank's part of this round must have landed in this rank's buffer before it is read
     sp.cols = reinterpret_cast<const double *>(f->xchg + (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes);
-    // ... which the sequential kernel waits for itself, after its prologue (no separate wait kernel)
-    sp.wait_flags = reinterpret_cast<const unsigned long long *>(f->xchg + 2 * f->xchg_cols_bytes);
-    sp.wait_count = f->cfg.shard_count;
-    sp.wait_round = f->xchg_round;
+    // ... element by element, as the sequential kernel reads them (no wait kernel, no flags on the critical path)
+    sp.cols_poll = 1;
   }
   sp.done_out = done_dev ? done_dev : f->done_dev;
   sp.bar = f->bar; sp.bar_base = f->bar_base;
@@ -216,10 +227,26 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   void *args[] = {(void *)&sp};
   const void *seq_fn = f->seq_threads == kSeqThreadsSmall ? (const void *)ekf_seq_kernel<kSeqThreadsSmall>
                                                           : (const void *)ekf_seq_kernel<kSeqThreadsLarge>;
-  CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
-                                    seq_smem_bytes(f->seq_threads, hot), f->stream));
+  if (f->pend_peer && env_int("EKF_SHARD_COOP_SEQ", 0) == 0) {
+    // PLAIN launch: a cooperative grid is held back until the device is otherwise idle, i.e. until the push kernel on
+    // the shard stream has finished - the very thing it is meant to overlap.  Co-residency, all the hand-written grid
+    // barrier needs, holds once the (short, never-waiting) push CTAs have left; the barrier's wait is bounded anyway:
+    // a grid that never becomes resident latches EKF_ERR_CUDA (and reports done = -1) instead of hanging the GPU.
+    sp.bar_timeout_ns = 12000000000ull;                      // above the 10 s bound of the peer wait inside
+    if (f->seq_threads == kSeqThreadsSmall)
+      ekf_seq_kernel<kSeqThreadsSmall><<<f->seq_grid, kSeqThreadsSmall, seq_smem_bytes(kSeqThreadsSmall, hot), f->stream>>>(sp);
+    else
+      ekf_seq_kernel<kSeqThreadsLarge><<<f->seq_grid, kSeqThreadsLarge, seq_smem_bytes(kSeqThreadsLarge, hot), f->stream>>>(sp);
+    CK(f, cudaGetLastError());
+  } else {
+    CK(f, cudaLaunchCooperativeKernel(seq_fn, dim3(f->seq_grid), dim3(f->seq_threads), args,
+                                      seq_smem_bytes(f->seq_threads, hot), f->stream));
+  }
   f->launches++;
   if (timed) CK(f, cudaEventRecord(f->ev[slot + 1], f->stream));
+  // the covariance pass rewrites Sigma in place: the push kernel of this round (shard stream) must have read its
+  // columns first - the sequential kernel only waited for the elements it used
+  const bool pushed = f->pend_peer != 0;
   // association / done / pose / count are final here: hand them to the host before the covariance pass
   if (results_bytes > 0)
     CK(f, cudaMemcpyAsync(results_host, results_dev, (size_t)results_bytes, cudaMemcpyDeviceToHost, f->stream));
@@ -234,6 +261,8 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
     CK(f, cudaEventRecord(f->shard_ev_seq, f->stream));
     CK(f, cudaStreamWaitEvent(f->shard_stream, f->shard_ev_seq, 0));
     pass_stream = f->shard_stream;
+  } else if (pushed) {
+    CK(f, cudaStreamWaitEvent(f->stream, f->shard_ev_push, 0));
   }
   DdParams dp{};
   dp.sigma = f->sigma; dp.V = f->V; dp.W = f->W;
@@ -254,6 +283,24 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   if (side) {
     CK(f, cudaEventRecord(f->shard_ev_pass, f->shard_stream));
     f->shard_pass_pending = true;
+  }
+  if (pushed) {
+    // recycling of this round's column buffer, on the shard stream behind the sequential kernel (and behind the pass
+    // when that runs there too): off the critical path
+    if (!side) {
+      CK(f, cudaEventRecord(f->shard_ev_seq, f->stream));
+      CK(f, cudaStreamWaitEvent(f->shard_stream, f->shard_ev_seq, 0));
+    }
+    PeerTable pt{};
+    pt.count = f->cfg.shard_count; pt.self = f->cfg.shard_rank;
+    for (int q = 0; q < pt.count; ++q)
+      pt.flags[q] = reinterpret_cast<unsigned long long *>(f->peer_base[q] + 2 * f->xchg_cols_bytes);
+    shard_recycle_kernel<<<64, 256, 0, f->shard_stream>>>(
+        reinterpret_cast<const unsigned long long *>(f->xchg + 2 * f->xchg_cols_bytes), pt, f->xchg_round,
+        reinterpret_cast<double *>(f->xchg + (size_t)(f->xchg_round & 1) * f->xchg_cols_bytes),
+        (int64_t)(f->xchg_cols_bytes / sizeof(double)), f->push_done + 1, f->status);
+    f->launches++;
+    CK(f, cudaGetLastError());
   }
   return EKF_OK;
 }

@@ -97,11 +97,10 @@ struct SeqParams {
   const double *cols;
   const int *guess;
   int *done_out;          // measurements actually processed (a failed speculation stops the scan early)
-  // peer-memory exchange: the columns of this round are complete once every rank's arrival flag has reached
-  // wait_round (ekf_shard.cuh); the kernel waits for them itself, after its prologue (nullptr: nothing to wait for)
-  const unsigned long long *wait_flags;
-  int wait_count;
-  unsigned long long wait_round;
+  // peer-memory exchange: `cols` is being filled by every rank's shard_push_cols_kernel WHILE this kernel runs; an
+  // element has arrived when neither of its halves is kColsSentinel any more (the buffer was poisoned before it was
+  // handed out).  0: `cols` is complete before the launch (caller's all-reduce, overlapped single-GPU mode).
+  int cols_poll;
   // grid barrier + arg-min slots
   unsigned long long *bar;
   unsigned long long bar_base;
@@ -189,6 +188,30 @@ __device__ __forceinline__ double4 ldcg_d4(const double4 *p) {
   asm volatile("ld.global.cg.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
   asm volatile("ld.global.cg.v2.f64 {%0,%1}, [%2];" : "=d"(v.z), "=d"(v.w) : "l"((const double *)p + 2));
   return v;
+}
+
+// Flag-in-data arrival of the exchanged columns (row-sharded path, ekf_shard.cuh): a column buffer is filled with this
+// pattern before it is handed out - a NaN no arithmetic produces (the hardware's NaNs are canonical) - and the owner's
+// stores replace it.  Both 32-bit halves are equal so that any fill granularity works.
+constexpr unsigned long long kColsSentinel = 0xFFF1FFF1FFF1FFF1ull;
+// the four doubles (rows a, a + 1 of one slot) at src, once they have arrived; bounded (a peer that never delivers
+// latches EKF_ERR_CUDA after ~10 s and lets the kernel run on with the NaNs instead of hanging the GPU)
+__device__ __forceinline__ void poll_cols(const double *src, double2 &r0, double2 &r1, int *status) {
+  unsigned long long b0, b1, b2, b3, t0 = 0;
+  unsigned polls = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(b0), "=l"(b1) : "l"(src) : "memory");
+    asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(b2), "=l"(b3) : "l"(src + 2) : "memory");
+    if (b0 != kColsSentinel && b1 != kColsSentinel && b2 != kColsSentinel && b3 != kColsSentinel) break;
+    if ((++polls & 255u) == 0) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 >= 10000000000ull) { atomicMax(status, 5 /* EKF_ERR_CUDA */); break; }
+    }
+  }
+  r0 = make_double2(__longlong_as_double((long long)b0), __longlong_as_double((long long)b1));
+  r1 = make_double2(__longlong_as_double((long long)b2), __longlong_as_double((long long)b3));
 }
 
 // Shared per-measurement broadcast: the chosen landmark and its update record.
@@ -340,22 +363,6 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
     }
   }
 
-  // the exchanged columns of this round: every rank's arrival flag (system-scope acquire; bounded like
-  // shard_wait_peers_kernel - a peer that never arrives latches EKF_ERR_CUDA after ~10 s instead of hanging)
-  if (p.wait_flags != nullptr) {
-    if (tid < p.wait_count) {
-      unsigned long long t0, now, v;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-      for (;;) {
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p.wait_flags + tid) : "memory");
-        if (v >= p.wait_round) break;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (now - t0 >= 10000000000ull) { atomicMax(p.status, kErrCuda); break; }
-      }
-    }
-    __syncthreads();
-  }
-
   // ---------------- measurement loop --------------------------------------------------------
   const bool unknown = (p.ids == nullptr);
   const int G = (int)gridDim.x;
@@ -471,7 +478,7 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
       // part of the grid never became resident: report instead of spinning (the host resets the counter)
       if (tid == 0) {
         atomicMax(p.status, kErrCuda);
-        if (p.done_out) atomicExch(p.done_out, -1);
+        if (p.done_out) *(volatile int *)p.done_out = -1;   // (plain store: done_out may be mapped pinned host memory)
       }
       return;
     }
@@ -737,8 +744,13 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
           if (p.cols != nullptr) {
             if (slot >= 0) {             // exchanged raw columns, [slot][row][2]
               const double *src = p.cols + ((int64_t)slot * n_pad + a) * 2;
-              const double2 r0 = __ldcg(reinterpret_cast<const double2 *>(src));
-              const double2 r1 = __ldcg(reinterpret_cast<const double2 *>(src + 2));
+              double2 r0, r1;
+              if (p.cols_poll) {
+                poll_cols(src, r0, r1, p.status);
+              } else {
+                r0 = __ldcg(reinterpret_cast<const double2 *>(src));
+                r1 = __ldcg(reinterpret_cast<const double2 *>(src + 2));
+              }
               q00 = r0.x; q01 = r0.y; q10 = r1.x; q11 = r1.y;
             } else {                     // landmark created in this scan: Sigma_0 column is zero
               q00 = 0.0; q01 = 0.0; q10 = 0.0; q11 = 0.0;
@@ -864,7 +876,7 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
     } else if (grid_barrier_bounded(p.bar, p.bar_base + gridDim.x, p.bar_timeout_ns)) {
       if (tid == 0) {
         atomicMax(p.status, kErrCuda);
-        if (p.done_out) atomicExch(p.done_out, -1);
+        if (p.done_out) *(volatile int *)p.done_out = -1;   // (plain store: done_out may be mapped pinned host memory)
       }
       return;
     }

@@ -218,80 +218,28 @@ struct PeerTable {
   double *cols[kMaxPeers];                 // this round's column buffer of every rank
   unsigned long long *flags[kMaxPeers];    // flag array of every rank: flags[q][g] = rounds rank g has pushed to q
 };
-// One thread per ROW, all m slots: a thread first gathers its (up to 8 at a time) owned elements, then stores them to
-// every rank - the loads of a batch are in flight together (the compiler cannot hoist them over the peer stores
-// itself: the pointers may alias).  One arrival ticket per CTA: with a thread per (slot, row) the 1,580 same-address
-// atomics of the tickets alone took ~10 us (profiles/r2h_shard_launches_R8.csv).
+// One thread per ROW, all m slots, 8 at a time: a thread first gathers its owned elements of a batch (loads in flight
+// together - the compiler cannot hoist them over the peer stores itself: the pointers may alias), then stores them to
+// every rank.  The CONSUMER does not wait for this kernel: the sequential kernel runs concurrently (other stream) and
+// polls the very elements it needs - every column buffer is filled with kColsSentinel before it is handed out, and an
+// element is there when neither of its halves is the sentinel any more (flag-in-data, the low-latency protocol of
+// collective libraries).  What the fences, tickets and flags at the END of this kernel are for is buffer RECYCLING,
+// off the critical path: shard_recycle_kernel re-poisons a buffer only after every rank's push of that round has
+// completely landed, and this kernel writes into a peer's buffer only after that peer has released it (credit).
+//
+// TWO HOPS for the row segment (two_hop != 0; more than two ranks).  The rank that stores row a of a sighted landmark
+// owns the whole segment (i < a) of that slot: delivered directly it ships ~22 MB per scan at 8 GPUs, N = 10,000,
+// m = 20, while the other ranks ship a few hundred KB - 56 us for that one push kernel, and every sequential kernel
+// waits for it (bench.py run.per_rank, profiles/r2l_bench8.json).  So the segment travels the way an all-gather
+// balances its links: 128-row blocks are assigned to RELAY ranks block-cyclically (block b -> rank b % R); the owner
+// stores block b to itself and to the relay only; the relay's CTA of that block polls its own buffer (flag-in-data
+// again) and forwards each element to the remaining ranks as it lands.  The column part (i > a + 1) is spread over
+// the ranks already and goes out directly.
 constexpr int kPushThreads = 128;
+static_assert(kPushThreads == EKF_STRIP, "one CTA per 128-row block (relay assignment)");
 __global__ void __launch_bounds__(kPushThreads) shard_push_cols_kernel(
     const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m, PeerTable peers,
-    unsigned long long round_no, unsigned int *done_ctas) {
-  __shared__ int s_guess[32];
-  __shared__ unsigned int s_prev;
-  if (threadIdx.x < 32) s_guess[threadIdx.x] = (int)threadIdx.x < m ? guess[threadIdx.x] : -1;
-  __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool own_i = i < n_pad && ekf_lay_owns_row(lay, i);
-  bool any = false;
-  for (int s0 = 0; s0 < m; s0 += 8) {
-    double2 v[8];
-    bool st[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      st[u] = false;
-      const int slot = s0 + u;
-      const int j = slot < m ? s_guess[slot] : -1;
-      if (j < 0 || j >= N || i >= n_pad) continue;
-      const int a = 4 + 2 * j;
-      if (i > a + 1) {
-        if (own_i) { v[u] = *reinterpret_cast<const double2 *>(sigma + ekf_lay_elem(lay, i, a)); st[u] = true; }
-      } else if (i < a) {
-        if (ekf_lay_owns_row(lay, a)) {
-          v[u].x = sigma[ekf_lay_elem(lay, a, i)];
-          v[u].y = sigma[ekf_lay_elem(lay, a + 1, i)];
-          st[u] = true;
-        }
-      }                                    // (the landmark's own 2 x 2 block comes from D, not from here)
-    }
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      if (!st[u]) continue;
-      any = true;
-      const int64_t e = (int64_t)(s0 + u) * n_pad + i;
-      for (int q = 0; q < peers.count; ++q) *reinterpret_cast<double2 *>(peers.cols[q] + e * 2) = v[u];
-    }
-  }
-  // arrival: every CTA's stores are visible system-wide before the flags move
-  if (__syncthreads_or(any ? 1 : 0)) __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) s_prev = atomicAdd(done_ctas, 1u);
-  __syncthreads();
-  if (s_prev == gridDim.x - 1) {
-    if (threadIdx.x == 0) *done_ctas = 0;                    // ready for the next launch
-    __threadfence_system();
-    if ((int)threadIdx.x < peers.count) {
-      unsigned long long *dst = peers.flags[threadIdx.x] + peers.self;
-      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(round_no) : "memory");
-    }
-  }
-}
-// ---- two-hop delivery (one process per GPU) ----------------------------------------------------------------------
-// In shard_push_cols_kernel the rank that stores row a of a sighted landmark ships the whole row segment (i < a) of
-// every slot to every peer: at 8 GPUs, N = 10,000, m = 20 that one rank stores ~22 MB over NVLink per scan while the
-// others ship a few hundred KB, and the other seven sequential kernels wait 30-40 us for it (bench.py run.per_rank).
-// Here the row segment travels in two hops, the way an all-gather balances its links: 128-row blocks are assigned to
-// RELAY ranks block-cyclically (block b -> rank b % R); hop 1: the owner stores block b's elements to itself and to
-// the relay only (3.2 MB out instead of 22); hop 2: the relay forwards what arrived to the remaining ranks (every rank
-// forwards ~1/R of the segment).  The column part (i > a + 1, stored by the rank that owns row i) is spread over the
-// ranks already and is delivered directly, as before.  One kernel: CTA b = row block b; after hop 1 the rank raises
-// its hop-1 flag everywhere; the relay CTAs (b % R == self) wait for every rank's hop-1 flag of this round (bounded),
-// forward, and the last CTA raises the arrival flag the sequential kernel waits for.  Needs every rank's push kernel
-// to make progress independently (one stream per rank): handles of ONE process that share a stream keep the direct
-// kernel (ekf_abi_shard.inl).
-static_assert(kPushThreads == EKF_STRIP, "one CTA per 128-row block");
-__global__ void __launch_bounds__(kPushThreads) shard_push_cols_2hop_kernel(
-    const double *sigma, EkfLay lay, int n_pad, int N, const int *guess, int m, PeerTable peers,
-    PeerTable hop1, unsigned long long round_no, unsigned int *tickets, int *status) {
+    const unsigned long long *credits, unsigned long long round_no, unsigned int *done_ctas, int *status, int two_hop) {
   __shared__ int s_guess[32], s_owner[32];
   __shared__ unsigned int s_prev;
   const int R = peers.count, self = peers.self;
@@ -306,14 +254,26 @@ __global__ void __launch_bounds__(kPushThreads) shard_push_cols_2hop_kernel(
     }
     s_owner[threadIdx.x] = own;
   }
+  // credit: rank q has re-poisoned the buffer this round writes into (the one of round_no - 2); two rounds old, so
+  // this never waits in practice.  Bounded like every cross-GPU wait here.
+  if ((int)threadIdx.x < R && round_no > 2) {
+    unsigned long long t0, now, v;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(credits + threadIdx.x) : "memory");
+      if (v + 2 >= round_no) break;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (now - t0 >= 10000000000ull) { atomicMax(status, kErrPeerTimeout); break; }
+    }
+  }
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int relay = (int)(blockIdx.x % (unsigned)R);
+  const int relay = two_hop ? (int)(blockIdx.x % (unsigned)R) : self;
   const bool own_i = i < n_pad && ekf_lay_owns_row(lay, i);
   bool any = false;
   for (int s0 = 0; s0 < m; s0 += 8) {
     double2 v[8];
-    int kind[8];                                             // 0 nothing, 1 column part (to all), 2 row segment (hop 1)
+    int kind[8];                                             // 0 nothing, 1 column part, 2 row segment
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       kind[u] = 0;
@@ -329,14 +289,14 @@ __global__ void __launch_bounds__(kPushThreads) shard_push_cols_2hop_kernel(
           v[u].y = sigma[ekf_lay_elem(lay, a + 1, i)];
           kind[u] = 2;
         }
-      }
+      }                                    // (the landmark's own 2 x 2 block comes from D, not from here)
     }
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       if (kind[u] == 0) continue;
       any = true;
       const int64_t e = ((int64_t)(s0 + u) * n_pad + i) * 2;
-      if (kind[u] == 1 || relay == self) {                   // direct: every rank (the owner relays this block itself)
+      if (kind[u] == 1 || !two_hop || relay == self) {       // direct: every rank (an owner relays its own blocks itself)
         for (int q = 0; q < R; ++q) *reinterpret_cast<double2 *>(peers.cols[q] + e) = v[u];
       } else {                                               // hop 1: own copy + the relay's
         *reinterpret_cast<double2 *>(peers.cols[self] + e) = v[u];
@@ -344,52 +304,57 @@ __global__ void __launch_bounds__(kPushThreads) shard_push_cols_2hop_kernel(
       }
     }
   }
-  // hop-1 arrival: this rank's stores are visible system-wide before its hop-1 flag moves
+  // hop 2: this rank relays the block: forward what the other owners leave in its buffer as it lands.  All slots of a
+  // batch are polled together (independent loads in flight), not one after the other: a poll is an L2 round trip
+  if (two_hop && relay == self && i < n_pad) {
+    for (int s0 = 0; s0 < m; s0 += 8) {
+      unsigned pending = 0;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int slot = s0 + u;
+        if (slot >= m) continue;
+        const int j = s_guess[slot], own = s_owner[slot];
+        if (j < 0 || j >= N || own < 0 || own == self || i >= 4 + 2 * j) continue;
+        pending |= 1u << u;
+      }
+      unsigned long long t0 = 0;
+      unsigned polls = 0;
+      while (pending) {
+        unsigned long long b0[8], b1[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (!((pending >> u) & 1u)) continue;
+          const double *src = peers.cols[self] + ((int64_t)(s0 + u) * n_pad + i) * 2;
+          asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(b0[u]), "=l"(b1[u]) : "l"(src) : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (!((pending >> u) & 1u)) continue;
+          if (b0[u] == kColsSentinel || b1[u] == kColsSentinel) continue;
+          const int64_t e = ((int64_t)(s0 + u) * n_pad + i) * 2;
+          const int own = s_owner[s0 + u];
+          const double2 w = make_double2(__longlong_as_double((long long)b0[u]), __longlong_as_double((long long)b1[u]));
+          for (int q = 0; q < R; ++q)
+            if (q != self && q != own) *reinterpret_cast<double2 *>(peers.cols[q] + e) = w;
+          pending &= ~(1u << u);
+          any = true;
+        }
+        if (pending && (++polls & 63u) == 0) {
+          unsigned long long now;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+          if (t0 == 0) t0 = now;
+          else if (now - t0 >= 10000000000ull) { atomicMax(status, kErrPeerTimeout); break; }
+        }
+      }
+    }
+  }
+  // completion (for the recycling only): every CTA's stores are visible system-wide before the flags move
   if (__syncthreads_or(any ? 1 : 0)) __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) s_prev = atomicAdd(tickets, 1u);
+  if (threadIdx.x == 0) s_prev = atomicAdd(done_ctas, 1u);
   __syncthreads();
   if (s_prev == gridDim.x - 1) {
-    if (threadIdx.x == 0) tickets[0] = 0;
-    __threadfence_system();
-    if ((int)threadIdx.x < R) {
-      unsigned long long *dst = hop1.flags[threadIdx.x] + self;
-      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(round_no) : "memory");
-    }
-  }
-  // hop 2: the relay CTAs forward what the other owners left in this rank's buffer
-  bool fwd = false;
-  if (relay == self) {
-    if ((int)threadIdx.x < R) {
-      unsigned long long t0, now, f;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-      for (;;) {
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(f) : "l"(hop1.flags[self] + threadIdx.x) : "memory");
-        if (f >= round_no) break;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (now - t0 >= 10000000000ull) { atomicMax(status, kErrPeerTimeout); break; }
-      }
-    }
-    __syncthreads();
-    if (i < n_pad) {
-      for (int slot = 0; slot < m; ++slot) {
-        const int j = s_guess[slot], own = s_owner[slot];
-        if (j < 0 || j >= N || own < 0 || own == self) continue;
-        if (i >= 4 + 2 * j) continue;
-        const int64_t e = ((int64_t)slot * n_pad + i) * 2;
-        const double2 w = __ldcg(reinterpret_cast<const double2 *>(peers.cols[self] + e));
-        for (int q = 0; q < R; ++q)
-          if (q != self && q != own) *reinterpret_cast<double2 *>(peers.cols[q] + e) = w;
-        fwd = true;
-      }
-    }
-  }
-  if (__syncthreads_or(fwd ? 1 : 0)) __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) s_prev = atomicAdd(tickets + 1, 1u);
-  __syncthreads();
-  if (s_prev == gridDim.x - 1) {
-    if (threadIdx.x == 0) tickets[1] = 0;
+    if (threadIdx.x == 0) *done_ctas = 0;                    // ready for the next launch
     __threadfence_system();
     if ((int)threadIdx.x < R) {
       unsigned long long *dst = peers.flags[threadIdx.x] + self;
@@ -398,6 +363,44 @@ __global__ void __launch_bounds__(kPushThreads) shard_push_cols_2hop_kernel(
   }
 }
 
+// Recycling of this rank's column buffer of round `round_no`, on the shard stream after the sequential kernel that
+// read it: wait until EVERY rank's push of that round has completely landed here (their completion flags; a late
+// store after the re-poisoning would look like fresh data two rounds later), fill the buffer with the sentinel again,
+// then tell every rank that it may write round_no + 2 into it (credit).
+__global__ void __launch_bounds__(256) shard_recycle_kernel(const unsigned long long *flags, PeerTable peers,
+                                                            unsigned long long round_no, double *buf, int64_t doubles,
+                                                            unsigned int *ticket, int *status) {
+  __shared__ unsigned int s_prev;
+  if ((int)threadIdx.x < peers.count) {
+    unsigned long long t0, now, v;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + threadIdx.x) : "memory");
+      if (v >= round_no) break;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (now - t0 >= 10000000000ull) { atomicMax(status, kErrPeerTimeout); break; }
+    }
+  }
+  __syncthreads();
+  const double2 poison = make_double2(__longlong_as_double((long long)kColsSentinel),
+                                      __longlong_as_double((long long)kColsSentinel));
+  double2 *b2 = reinterpret_cast<double2 *>(buf);
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < doubles / 2; e += (int64_t)gridDim.x * blockDim.x)
+    b2[e] = poison;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_prev = atomicAdd(ticket, 1u);
+  __syncthreads();
+  if (s_prev == gridDim.x - 1) {
+    if (threadIdx.x == 0) *ticket = 0;
+    __threadfence_system();
+    if ((int)threadIdx.x < peers.count) {
+      // credit array of rank q sits behind its completion flags: credits[self] = last round this rank has released
+      unsigned long long *dst = peers.flags[threadIdx.x] + kMaxPeers + peers.self;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(round_no) : "memory");
+    }
+  }
+}
 // consumer side: wait until every rank has pushed round `round_no` into this rank's buffer.  Bounded: a peer
 // that never arrives (crashed process) latches kErrPeerTimeout after ~10 s instead of hanging the GPU.
 __global__ void shard_wait_peers_kernel(const unsigned long long *flags, int count, unsigned long long round_no,

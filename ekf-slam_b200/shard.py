@@ -98,6 +98,8 @@ class _Driver:
             if not check:
                 return rounds
             done = int(done_t.item())
+            if done < 0:
+                raise RuntimeError("sharded scan: the sequential kernel's grid barrier timed out (EKF_ERR_CUDA)")
             if done == 0 and rounds > 4 * m + 4:
                 raise RuntimeError("sharded scan makes no progress")
             t0 += done
@@ -164,6 +166,8 @@ class _Driver:
                 rounds += 1
                 first = False
                 done = int(hres[28:32].view(np.int32)[0])
+                if done < 0:
+                    raise RuntimeError("sharded scan: the sequential kernel's grid barrier timed out (EKF_ERR_CUDA)")
                 if done == 0 and rounds > 4 * m + 4:
                     raise RuntimeError("sharded scan makes no progress")
                 t0 += done

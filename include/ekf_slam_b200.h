@@ -184,6 +184,9 @@ int ekf_set_overlap(ekf_filter *f, int32_t on);
  * covariance pass.  A scan split into several passes (m > 24) counts once per pass. */
 int ekf_enable_timing(ekf_filter *f, int32_t ring_scans);
 int ekf_read_timing(ekf_filter *f, float *seq_ms, float *downdate_ms, int32_t max_scans, int32_t *n_scans);
+/* the same ring for the begin phase of the row-sharded path (ekf_shard_scan_begin): milliseconds of the speculative
+ * association kernel and of the peer-memory push kernel (0 when the round used the caller's all-reduce) */
+int ekf_read_timing_shard(ekf_filter *f, float *assoc_ms, float *push_ms, int32_t max_scans, int32_t *n_scans);
 
 /* ---- one large map row-sharded over several GPUs (BASELINE configs 4-5 at 2/4/8 GPUs) ------------
  * One process (or one handle) per GPU, created with cfg.shard_rank / cfg.shard_count: the handle
