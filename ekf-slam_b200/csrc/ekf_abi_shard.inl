@@ -227,7 +227,14 @@ int ekf_shard_scan_finish_ex(ekf_filter *f, int32_t *assoc_dev, int32_t *done_de
   void *args[] = {(void *)&sp};
   const void *seq_fn = f->seq_threads == kSeqThreadsSmall ? (const void *)ekf_seq_kernel<kSeqThreadsSmall>
                                                           : (const void *)ekf_seq_kernel<kSeqThreadsLarge>;
-  if (f->pend_peer && env_int("EKF_SHARD_COOP_SEQ", 0) == 0) {
+  // The overlap needs a push CTA (128 threads x 104 registers) to fit on an SM BESIDE the resident sequential CTAs:
+  // true for the 64-thread shape (2 x 64 x 244 registers), not for the 256-thread shape of large maps, whose CTAs
+  // fill the register file - there the push kernel would wait for the sequential kernel that polls for its data.
+  // Large maps therefore order the sequential kernel after the push (their passes take milliseconds; the exchange
+  // is noise), and keep the cooperative launch.
+  const bool overlap_push = f->pend_peer && f->seq_threads == kSeqThreadsSmall && env_int("EKF_SHARD_COOP_SEQ", 0) == 0;
+  if (f->pend_peer && !overlap_push) CK(f, cudaStreamWaitEvent(f->stream, f->shard_ev_push, 0));
+  if (overlap_push) {
     // PLAIN launch: a cooperative grid is held back until the device is otherwise idle, i.e. until the push kernel on
     // the shard stream has finished - the very thing it is meant to overlap.  Co-residency, all the hand-written grid
     // barrier needs, holds once the (short, never-waiting) push CTAs have left; the barrier's wait is bounded anyway:

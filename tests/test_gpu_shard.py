@@ -158,3 +158,39 @@ def test_sharded_handle_refuses_the_single_handle_entry_points():
         ptr, cnt = C.c_void_p(), C.c_int64(0)
         # scan before the side state was synchronised
         assert L.ekf_shard_scan_begin(h._h, None, 1, C.c_void_p(8), None, 1, C.byref(ptr), C.byref(cnt)) == m.EKF_ERR_INVALID
+
+
+@pytest.mark.parametrize("threads", [64, 256])
+def test_device_resident_pipeline_both_sequential_shapes(threads, monkeypatch):
+    """scan_dev back to back without host round trips (what bench.py times), peer-memory exchange: the 64-thread
+    sequential shape runs concurrently with the push kernel and polls its columns (flag-in-data), the 256-thread shape
+    of large maps cannot share an SM with the push CTAs and is ordered after it.  Same numbers as the host loop."""
+    import torch
+    from ekf_slam_b200 import shard
+    monkeypatch.setenv("EKF_SEQ_THREADS", str(threads))
+    N, count, m, scans = 300, 290, 20, 6
+    g, o, grid_w = _pair(N, count, 3, peer=True)
+    rng = np.random.default_rng(5)
+    pose = np.array([0.3, grid_w / 2.0, grid_w / 2.0])
+    g.set_previous_xy(pose[1], pose[2]); o.set_prev(pose[1], pose[2])
+    poses, xys, want = [], [], []
+    for s in range(scans):
+        pose = pose + np.array([0.05, 0.1, 0.07])
+        near, xy = _scan_inputs(o.state, count, rng, m, pose)
+        o.predict(*pose)
+        want.append(list(o.update_unknown(xy)))
+        poses.append(pose.copy()); xys.append(xy)
+    with torch.cuda.stream(g.stream):
+        d_pose = torch.from_numpy(np.array(poses)).cuda()
+        d_xy = torch.from_numpy(np.array(xys)).cuda()
+        d_assoc = torch.full((scans, m), -9, dtype=torch.int32, device="cuda")
+        d_done = torch.zeros(scans, dtype=torch.int32, device="cuda")
+    for s in range(scans):
+        g.scan_dev(d_pose[s], d_xy[s], d_assoc[s], check=False, done_t=d_done[s:s + 1])
+    torch.cuda.synchronize()
+    assert d_done.cpu().tolist() == [m] * scans
+    assert d_assoc.cpu().numpy().tolist() == want
+    assert g.hs[0].last_status() == 0
+    assert rel_fro(g.state(), o.state) <= 1e-9
+    assert rel_fro(g.sigma(), o.sigma) <= 1e-9
+    g.close(); o.close()
