@@ -8,9 +8,11 @@
 //                        speculative association of all m sightings against the scan-start state
 //                        -> guess[t]; every rank writes the part it owns of the raw Sigma_0 columns
 //                        of the guessed landmarks into the exchange buffer (zeros elsewhere)
-//   caller               sum-all-reduce of the buffer (NCCL over NVLink / NVSwitch; m * n_pad * 2
-//                        doubles = 6.4 MB at N = 10,000, m = 20).  Each element has exactly one
-//                        non-zero contributor, so the sum is exact.
+//   exchange             every used element of the buffer has exactly one owner, so nothing is reduced, only
+//                        delivered: by shard_push_cols_kernel over peer memory (NVLink / NVSwitch stores,
+//                        flag-in-data arrival, two-hop relay; concurrent with the sequential kernel), or by the
+//                        caller's sum-all-reduce (NCCL; m * n_pad * 2 doubles = 6.4 MB at N = 10,000, m = 20; exact,
+//                        because all but one contributor are zero)
 //   finish  (ekf_seq.cuh + ekf_downdate.cuh)  the unchanged sequential phase, replicated, reading
 //                        the columns from the buffer instead of Sigma; it re-derives every association
 //                        with the reference's sequential semantics and STOPS if a decision ever needs

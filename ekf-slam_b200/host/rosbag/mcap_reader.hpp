@@ -120,6 +120,7 @@ public:
     return s;
   }
   void skip_str() {const uint32_t k = get<uint32_t>(); need(k); i_ += k;}
+  size_t left() const {return n_ - i_;}
   template<class T> std::vector<T> seq()
   {
     const uint32_t k = get<uint32_t>();
@@ -195,18 +196,21 @@ inline MarkerArrayMsg decode_marker_array(const uint8_t * p, size_t n)
     c.get<int32_t>(); c.get<uint32_t>();            // lifetime
     c.get<uint8_t>();                               // frame_locked
     {                                               // geometry_msgs/Point[] points (3 f64 each)
-      const uint32_t k = c.get<uint32_t>();
-      for (uint32_t q = 0; q < k; ++q) {c.get<double>(); c.get<double>(); c.get<double>();}
+      const size_t k = c.get<uint32_t>();            // (counts are checked against what is left: a corrupt count
+      if (k > c.left() / 24) {throw std::runtime_error("mcap: Marker.points count runs past the message");}   // must not wrap)
+      for (size_t q = 0; q < k; ++q) {c.get<double>(); c.get<double>(); c.get<double>();}
     }
     {                                               // std_msgs/ColorRGBA[] colors (4 f32 each)
-      const uint32_t k = c.get<uint32_t>();
-      for (uint32_t q = 0; q < 4 * k; ++q) {c.get<float>();}
+      const size_t k = c.get<uint32_t>();
+      if (k > c.left() / 16) {throw std::runtime_error("mcap: Marker.colors count runs past the message");}
+      for (size_t q = 0; q < 4 * k; ++q) {c.get<float>();}
     }
     c.skip_str();                                   // texture_resource
     c.skip_header(); c.skip_str(); c.skip_seq<uint8_t>();   // texture
     {                                               // UVCoordinate[] (2 f32 each)
-      const uint32_t k = c.get<uint32_t>();
-      for (uint32_t q = 0; q < 2 * k; ++q) {c.get<float>();}
+      const size_t k = c.get<uint32_t>();
+      if (k > c.left() / 8) {throw std::runtime_error("mcap: Marker.uv_coordinates count runs past the message");}
+      for (size_t q = 0; q < 2 * k; ++q) {c.get<float>();}
     }
     c.skip_str();                                   // text
     c.skip_str();                                   // mesh_resource
@@ -222,7 +226,11 @@ inline std::vector<uint8_t> decompress_chunk(
   const std::string & method, const uint8_t * src, size_t n, uint64_t uncompressed_size)
 {
   if (method.empty()) {return std::vector<uint8_t>(src, src + n);}
-  if (uncompressed_size > (uint64_t(1) << 32)) {throw std::runtime_error("mcap: chunk larger than 4 GiB");}
+  // a chunk states its own uncompressed size: bound it before allocating (rosbag2's default chunk is 4 MiB; zstd / lz4
+  // do not expand a block by more than a few thousand times), so that a tiny corrupt file cannot ask for gigabytes
+  if (uncompressed_size > (uint64_t(1) << 30) || uncompressed_size > (uint64_t(n) + 64) * 4096) {
+    throw std::runtime_error("mcap: implausible uncompressed chunk size");
+  }
   std::vector<uint8_t> out(static_cast<size_t>(uncompressed_size));
   if (method == "zstd") {
     static void * lib = dlopen("libzstd.so.1", RTLD_NOW | RTLD_LOCAL);

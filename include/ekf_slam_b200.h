@@ -213,11 +213,13 @@ int ekf_shard_info(ekf_filter *f, int32_t *row_begin, int32_t *row_end, int64_t 
 /* Optional: the per-scan exchange over peer memory instead of the caller's all-reduce.  Every rank exports
  * its exchange region (a CUDA IPC handle for other processes, the plain device pointer for handles of the
  * same process) and attaches every other rank's (exactly one of ipc_handle_64 / same_process_base per
- * call).  Once all shard_count - 1 peers are attached, ekf_shard_scan_begin extracts AND delivers in one
- * kernel - every rank stores the Sigma columns it owns straight into every rank's buffer over NVLink and
- * raises an arrival flag there - and returns *xchg_doubles = 0: there is nothing left to reduce;
- * ekf_shard_scan_finish waits for the flags on the device.  A peer that never arrives latches EKF_ERR_CUDA
- * after 10 s instead of hanging.  ekf_shard_sync_* still uses the caller's all-reduce (rare). */
+ * call).  Once all shard_count - 1 peers are attached, ekf_shard_scan_begin launches the delivery itself, on the
+ * handle's own side stream - every rank stores the Sigma columns it owns straight into every rank's buffer over
+ * NVLink (through a relay rank when there are more than two) - and returns *xchg_doubles = 0: there is nothing left
+ * to reduce.  The sequential kernel of ekf_shard_scan_finish runs concurrently and polls the elements it needs
+ * (every buffer is pre-filled with a sentinel).  A peer that never delivers latches EKF_ERR_CUDA after 10 s instead
+ * of hanging; *done_dev = -1 reports that the sequential kernel's own (bounded) grid barrier gave up.
+ * ekf_shard_sync_* still uses the caller's all-reduce (rare). */
 int ekf_shard_peer_export(ekf_filter *f, void *ipc_handle_64, void **local_base, int64_t *region_bytes);
 int ekf_shard_peer_attach(ekf_filter *f, int32_t peer_rank, const void *ipc_handle_64, void *same_process_base);
 int ekf_shard_sync_begin(ekf_filter *f, double **xchg_dev, int64_t *xchg_doubles);
