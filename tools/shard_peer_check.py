@@ -19,7 +19,7 @@ import bench  # noqa: E402
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-N, m, K = 3000, 20, 6
+N, m, K = 3000, 20, int(os.environ.get("SHARD_CHECK_SCANS", "6"))    # SHARD_CHECK_SCANS=3000: soak of the exchange
 side = int(np.ceil(np.sqrt(N)))
 out = []
 for peer in (True, False):
@@ -28,8 +28,22 @@ for peer in (True, False):
     drv.sync()
     poses, xy, ids = bench.make_workload(drv.h.state(), N - 8, m, K, 107)
     xy[-1, :3] += 0.45                                   # the last scan also creates landmarks
+    if K > 8:
+        xy[K // 2, :2] -= 0.45                           # ... and so does one in the middle of a soak
     drv.h.set_previous_xy(poses[0][1], poses[0][2])
-    assoc = [drv.scan(poses[s], xy[s])[0] for s in range(K)]
+    if K <= 8:
+        assoc = [drv.scan(poses[s], xy[s])[0] for s in range(K)]
+    else:
+        # soak: device-resident, back to back, no host round trip between scans (what bench.py times) - the exchange's
+        # buffer recycling (completion flags, credits, sentinel) is exercised at full rate
+        d_pose, d_xy = torch.from_numpy(poses).cuda(), torch.from_numpy(xy).cuda()
+        d_assoc = torch.full((K, m), -9, dtype=torch.int32, device="cuda")
+        d_done = torch.zeros(K, dtype=torch.int32, device="cuda")
+        for s in range(K):
+            drv.scan_dev(d_pose[s], d_xy[s], d_assoc[s], check=False, done_t=d_done[s:s + 1])
+        torch.cuda.synchronize()
+        assert bool((d_done == m).all()), "a round stopped early"
+        assoc = d_assoc.cpu().numpy()
     rb, re, _ = drv.h.shard_info() if hasattr(drv.h, "shard_info") else (0, 0, 0)
     rows = drv.h.sigma_block(0, drv.h.n, 0, drv.h.n)
     out.append((np.array(assoc), drv.h.state().copy(), rows.copy(), drv.h.last_status()))
@@ -40,7 +54,7 @@ flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
     print("peer-memory exchange == all-reduce exchange on every rank:", bool(flag.item()),
-          "| new landmarks in the last scan:", int((a1[-1] >= N - 8).sum()), "| non-zero Sigma entries held by rank 0:",
+          "| scans:", K, "| new landmarks in the last scan:", int((a1[-1] >= N - 8).sum()), "| non-zero Sigma entries held by rank 0:",
           int(np.count_nonzero(r1)))
 dist.destroy_process_group()
 sys.exit(0 if flag.item() else 1)
