@@ -418,8 +418,9 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
         }
         best = nb;
       }
-      const Cand wbest = warp_argmin(best);
-      if (best.k == wbest.k && best.k != 0x7fffffff) {
+      int wsrc;
+      const Cand wbest = warp_argmin_redux(best, wsrc);
+      if (lane == wsrc && best.k != 0x7fffffff) {
 #pragma unroll
         for (int i = 0; i < kRecDoubles; ++i) s_wrec[warp][i] = rec[i];
       }
@@ -530,15 +531,10 @@ __global__ void __launch_bounds__(NT, EKF_SEQ_MINB) ekf_seq_kernel(const SeqPara
             c = n2;
           }
         }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-          Cand o;
-          o.d = __shfl_xor_sync(0xffffffffu, c.d, off);
-          o.k = __shfl_xor_sync(0xffffffffu, c.k, off);
-          const int ob = __shfl_xor_sync(0xffffffffu, bstar, off);
-          const Cand n2 = cand_min(c, o);
-          if (n2.k != c.k) bstar = ob;
-          c = n2;
+        {
+          int csrc;
+          c = warp_argmin_redux(c, csrc);
+          bstar = __shfl_sync(0xffffffffu, bstar, csrc);
         }
         SEQ_STAMP(7);
         // the tentative landmark sits last with distance == threshold and wins only on a
