@@ -20,8 +20,15 @@ def _traces(B, N, n_scans, seed0, max_range):
     return out
 
 
-def _run_batch(traces, N, known, **kw):
+def _run_batch(traces, N, known, repeat=1, **kw):
     import struct_oracle as so
+    if repeat > 1:        # every sighting `repeat` times in its scan (scans longer than a warp: m > 32)
+        import copy
+        traces = copy.deepcopy(traces)
+        for tr in traces:
+            for sc in tr:
+                sc.xy = np.concatenate([np.asarray(sc.xy).reshape(-1, 2)] * repeat)
+                sc.ids = np.concatenate([np.asarray(sc.ids, dtype=np.int32)] * repeat)
     B, n_scans = len(traces), len(traces[0])
     g = ekf_slam_b200.EkfBatch(B, n_landmarks=N, **kw)
     oracles = [so.StructEkf(n_landmarks=N, **kw) for _ in range(B)]
@@ -79,6 +86,11 @@ def _run_batch(traces, N, known, **kw):
 def test_batch_config3_shape_against_oracle_b(known):
     """N = 20 landmarks per filter (n = 43), ragged scans, 40 filters x 25 scans."""
     _run_batch(_traces(40, 20, 25, seed0=100, max_range=1.8), 20, known)
+
+
+def test_batch_scans_longer_than_a_warp():
+    """m > 32: the polar sightings no longer fit one register per lane and go through shared memory"""
+    _run_batch(_traces(6, 20, 8, seed0=700, max_range=1.8), 20, False, repeat=3)
 
 
 def test_batch_reference_size_n103():
