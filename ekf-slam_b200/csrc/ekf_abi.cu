@@ -14,6 +14,7 @@
 
 #include "../../include/ekf_slam_b200.h"
 #include "ekf_batch.cuh"
+#include "ekf_batch_reg.cuh"
 #include "ekf_downdate.cuh"
 #include "ekf_landmarks.cuh"
 #include "ekf_layout.h"

@@ -11,6 +11,7 @@ struct ekf_batch {
   int nblk = 0;
   unsigned short *soff = nullptr;   // shared-memory offset of every packed element (layout of this handle's variant)
   int variant = 0;               // bits 0-1: downdate shape DD (0, 1, 2), bit 2: one-pass association, bit 3: 20 CTAs/SM
+  // (7: covariance in registers for the whole scan, ekf_batch_reg.cuh - measured slower, kept selectable)
   // staging for the host-pointer step
   unsigned char *io_dev = nullptr, *io_host = nullptr, *res_dev = nullptr, *res_host = nullptr;
   size_t io_cap = 0, res_cap = 0;
@@ -26,7 +27,11 @@ struct ekf_batch {
 
 namespace {
 
+constexpr int kBatchVariantReg = 7;        // covariance in registers for the whole scan (ekf_batch_reg.cuh): n = 41 .. 48, m <= 32
+constexpr int kBatchRegMinBlocks = 12;     // resident one-warp CTAs per SM (3 warps per scheduler: 168 registers each)
 constexpr int BATCH_DEFAULT_VARIANT = 6;   // one-pass association + DMMA 8x8-tile downdate, 16 CTAs/SM (measured best)
+
+inline int batch_dd(const ekf_batch *b) { return b->variant == kBatchVariantReg ? 2 : (b->variant & 3); }
 
 #define CKB(b, call)                                                               \
   do {                                                                             \
@@ -50,11 +55,17 @@ int batch_launch(ekf_batch *b, const double *poses, int m, const double *xy, con
   p.tri_map = b->tri_map; p.blk_map = b->blk_map; p.nblk = b->nblk; p.soff = b->soff;
   p.pose = poses; p.xy = xy; p.ids = ids; p.m_count = m_count; p.m = m;
   p.assoc_out = assoc; p.cnt_out = count; p.pose_out = pose_out;
-  const size_t smem = batch_smem_bytes(b->n, m, b->variant & 3);
+  const size_t smem = batch_smem_bytes(b->n, m, batch_dd(b));
   if (smem > 200 * 1024) return EKF_ERR_INVALID;   // m beyond the per-CTA shared memory
+  if (b->variant == kBatchVariantReg && m <= 32) {  // covariance in registers (ekf_batch_reg.cuh)
+    ekf_batch_reg_kernel<kBatchRegMinBlocks><<<nf, kBatchThreads, batch_reg_smem_bytes(), stream>>>(p);
+    b->launches++;
+    CKB(b, cudaGetLastError());
+    return EKF_OK;
+  }
 #define EKF_BATCH_CASE(V, MINB, ONE, DD) \
   case V: ekf_batch_kernel<MINB, ONE, DD><<<nf, kBatchThreads, smem, stream>>>(p); break;
-  switch (b->variant) {
+  switch (b->variant == kBatchVariantReg ? 6 : b->variant) {   // (longer scans of a register-shape handle: tiles)
     EKF_BATCH_CASE(0, 16, false, 0)  EKF_BATCH_CASE(1, 16, false, 1)  EKF_BATCH_CASE(2, 16, false, 2)
     EKF_BATCH_CASE(4, 16, true, 0)   EKF_BATCH_CASE(5, 16, true, 1)   EKF_BATCH_CASE(6, 16, true, 2)
     EKF_BATCH_CASE(8, 20, false, 0)  EKF_BATCH_CASE(9, 20, false, 1)  EKF_BATCH_CASE(10, 20, false, 2)
@@ -182,11 +193,12 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
     b->nblk = (int)blk.size();
     b->variant = BATCH_DEFAULT_VARIANT;
     if (const char *v = getenv("EKF_BATCH_VARIANT")) b->variant = atoi(v) & 15;   // development override
-    if ((b->variant & 3) == 3) b->variant &= ~1;
+    if (b->variant == kBatchVariantReg && !batch_reg_supported(b->N, b->n)) b->variant = 6;
+    if (b->variant != kBatchVariantReg && (b->variant & 3) == 3) b->variant &= ~1;
     if (b->N > 32) b->variant &= ~4;                                               // one-pass needs a lane per landmark
     std::vector<unsigned short> soff((size_t)b->tri);
     for (size_t q = 0; q < soff.size(); ++q)
-      soff[q] = (unsigned short)((b->variant & 3) == 2 ? batch_tile_idx(map[q].x, map[q].y)
+      soff[q] = (unsigned short)(batch_dd(b) == 2 ? batch_tile_idx(map[q].x, map[q].y)
                                                        : batch_row_off(map[q].x) + map[q].y);
     CKC(cudaMalloc(&b->soff, soff.size() * sizeof(unsigned short)));
     CKC(cudaMemcpy(b->soff, soff.data(), soff.size() * sizeof(unsigned short), cudaMemcpyHostToDevice));
@@ -212,6 +224,8 @@ int ekf_batch_create(const ekf_config *cfg, int32_t n_filters, ekf_batch **out) 
   EKF_BATCH_ATTR(20, false, 0) EKF_BATCH_ATTR(20, false, 1) EKF_BATCH_ATTR(20, false, 2)
   EKF_BATCH_ATTR(20, true, 0)  EKF_BATCH_ATTR(20, true, 1)  EKF_BATCH_ATTR(20, true, 2)
 #undef EKF_BATCH_ATTR
+  CKC(cudaFuncSetAttribute(ekf_batch_reg_kernel<kBatchRegMinBlocks>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                           cudaSharedmemCarveoutMaxShared));
   CKC(cudaStreamSynchronize(b->stream));
 #undef CKC
   *out = b;

@@ -155,3 +155,35 @@ def test_page_locked_caller_buffers_are_used_directly_and_give_the_same_filters(
         assert np.array_equal(a0, a1) and np.array_equal(c0, c1) and np.array_equal(q0, q1)
     assert np.array_equal(runs[0][1], runs[1][1]) and np.array_equal(runs[0][2], runs[1][2])
     assert int(runs[0][0][-1][1].min()) == N
+
+
+@pytest.mark.parametrize("known", [False, True])
+@pytest.mark.parametrize("N", [20, 22, 19])
+def test_register_resident_shape_leaves_the_same_filters_as_the_tile_shape(monkeypatch, known, N):
+    """EKF_BATCH_VARIANT=7 (ekf_batch_reg.cuh: the covariance stays in the warp's registers for the whole scan) against
+    the default tile shape on the same scans: landmarks discovered one scan at a time, ragged scans, re-sightings - same
+    arithmetic operation for operation, so associations, counters, states and covariances must be bit-identical."""
+    B = 80
+    fields = synth.batch_fields(B, N, seed=21)
+    runs = []
+    for variant in ("6", "7"):
+        monkeypatch.setenv("EKF_BATCH_VARIANT", variant)
+        g = ekf_slam_b200.EkfBatch(B, n_landmarks=N)
+        rr = np.random.default_rng(13)
+        outs = []
+        for s in range(12):
+            p = synth.batch_pose(B, s)
+            m = (5, 9, N, 12, N, 3, N, 16, N, N, 7, N)[s]
+            xy, order = synth.batch_scan(fields, p, rr, m=m)
+            mc = rr.integers(0, m + 1, size=B).astype(np.int32) if s % 3 == 1 else None
+            outs.append(g.step(p, xy, order if known else None, mc))
+        runs.append((outs, [g.state(f) for f in range(B)], [g.sigma(f) for f in range(B)]))
+        assert g.last_status() == 0
+        g.close()
+    for (a0, c0, q0), (a1, c1, q1) in zip(runs[0][0], runs[1][0]):
+        assert np.array_equal(a0, a1) and np.array_equal(c0, c1) and np.array_equal(q0, q1)
+    for f in range(B):
+        assert np.array_equal(runs[0][1][f], runs[1][1][f]), f
+        assert np.array_equal(runs[0][2][f], runs[1][2][f]), f
+    if not known:
+        assert int(runs[0][0][-1][1].max()) == N
