@@ -232,7 +232,7 @@ struct PeerTable {
 // TWO HOPS for the row segment (two_hop != 0; more than two ranks).  The rank that stores row a of a sighted landmark
 // owns the whole segment (i < a) of that slot: delivered directly it ships ~22 MB per scan at 8 GPUs, N = 10,000,
 // m = 20, while the other ranks ship a few hundred KB - 56 us for that one push kernel, and every sequential kernel
-// waits for it (bench.py run.per_rank, profiles/r2l_bench8.json).  So the segment travels the way an all-gather
+// waits for it (bench.py run.per_rank, profiles/r2l_bench8_flag_in_data_direct.json).  So the segment travels the way an all-gather
 // balances its links: 128-row blocks are assigned to RELAY ranks block-cyclically (block b -> rank b % R); the owner
 // stores block b to itself and to the relay only; the relay's CTA of that block polls its own buffer (flag-in-data
 // again) and forwards each element to the remaining ranks as it lands.  The column part (i > a + 1) is spread over
