@@ -3,6 +3,7 @@
 struct ekf_landmarks {
   int device = 0;
   int max_scans = 0, n_ranges = 0, max_out = 0;
+  int threads = 32;              // CTA size of ekf_landmarks_kernel (one CTA per scan)
   float *ranges_dev = nullptr;
   double *out_dev = nullptr;
   int *count_dev = nullptr, *status_dev = nullptr;
@@ -43,8 +44,17 @@ int ekf_landmarks_create(int32_t max_scans, int32_t n_ranges, int32_t max_out, i
             cudaMalloc(&h->out_dev, (size_t)max_scans * max_out * 3 * sizeof(double)) == cudaSuccess &&
             cudaMalloc(&h->count_dev, (size_t)max_scans * sizeof(int)) == cudaSuccess &&
             cudaMalloc(&h->status_dev, (size_t)max_scans * sizeof(int)) == cudaSuccess &&
-            cudaFuncSetAttribute(ekf_landmarks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            cudaFuncSetAttribute(ekf_landmarks_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)lm_smem_bytes(4096)) == cudaSuccess &&
+            cudaFuncSetAttribute(ekf_landmarks_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)lm_smem_bytes(4096)) == cudaSuccess &&
+            cudaFuncSetAttribute(ekf_landmarks_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)lm_smem_bytes(4096)) == cudaSuccess;
+  h->threads = kLmThreadsDefault;
+  if (const char *e = getenv("EKF_LM_THREADS")) {          // development override: 32, 64 or 128 threads per scan
+    const int t = atoi(e);
+    if (t == 32 || t == 64 || t == 128) h->threads = t;
+  }
   if (!ok) { ekf_landmarks_destroy(h); return EKF_ERR_CUDA; }
   *out = h;
   return EKF_OK;
@@ -60,7 +70,10 @@ int ekf_landmarks_detect_dev(ekf_landmarks *h, int32_t n_scans, const float *ran
   p.angle_min = angle_min; p.angle_increment = angle_increment; p.thr = cluster_threshold;
   p.out = out_xyr_dev; p.count = out_count_dev; p.status = out_status_dev;
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
-  ekf_landmarks_kernel<<<n_scans, kLmThreads, lm_smem_bytes(h->n_ranges), st>>>(p);
+  const size_t smem = lm_smem_bytes(h->n_ranges);
+  if (h->threads == 128) ekf_landmarks_kernel<128><<<n_scans, 128, smem, st>>>(p);
+  else if (h->threads == 64) ekf_landmarks_kernel<64><<<n_scans, 64, smem, st>>>(p);
+  else ekf_landmarks_kernel<32><<<n_scans, 32, smem, st>>>(p);
   h->launches++;
   return cudaGetLastError() == cudaSuccess ? EKF_OK : EKF_ERR_CUDA;
 }
