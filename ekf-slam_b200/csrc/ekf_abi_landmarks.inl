@@ -3,8 +3,8 @@
 struct ekf_landmarks {
   int device = 0;
   int max_scans = 0, n_ranges = 0, max_out = 0;
-  int threads = 32;              // CTA size of ekf_landmarks_kernel (one CTA per scan)
   float *ranges_dev = nullptr;
+  double2 *beam_dev = nullptr;   // (cos, sin) of the beam angles of the current call
   double *out_dev = nullptr;
   int *count_dev = nullptr, *status_dev = nullptr;
   cudaStream_t stream = nullptr;
@@ -18,7 +18,7 @@ int ekf_landmarks_destroy(ekf_landmarks *h) {
   {
     DeviceGuard guard(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    cudaFree(h->ranges_dev); cudaFree(h->out_dev); cudaFree(h->count_dev); cudaFree(h->status_dev);
+    cudaFree(h->ranges_dev); cudaFree(h->beam_dev); cudaFree(h->out_dev); cudaFree(h->count_dev); cudaFree(h->status_dev);
     if (h->stream) cudaStreamDestroy(h->stream);
   }
   delete h;
@@ -44,17 +44,11 @@ int ekf_landmarks_create(int32_t max_scans, int32_t n_ranges, int32_t max_out, i
             cudaMalloc(&h->out_dev, (size_t)max_scans * max_out * 3 * sizeof(double)) == cudaSuccess &&
             cudaMalloc(&h->count_dev, (size_t)max_scans * sizeof(int)) == cudaSuccess &&
             cudaMalloc(&h->status_dev, (size_t)max_scans * sizeof(int)) == cudaSuccess &&
-            cudaFuncSetAttribute(ekf_landmarks_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            cudaMalloc(&h->beam_dev, (size_t)n_ranges * sizeof(double2)) == cudaSuccess &&
+            cudaFuncSetAttribute(ekf_landmarks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)lm_smem_bytes(4096)) == cudaSuccess &&
-            cudaFuncSetAttribute(ekf_landmarks_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)lm_smem_bytes(4096)) == cudaSuccess &&
-            cudaFuncSetAttribute(ekf_landmarks_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)lm_smem_bytes(4096)) == cudaSuccess;
-  h->threads = kLmThreadsDefault;
-  if (const char *e = getenv("EKF_LM_THREADS")) {          // development override: 32, 64 or 128 threads per scan
-    const int t = atoi(e);
-    if (t == 32 || t == 64 || t == 128) h->threads = t;
-  }
+            cudaFuncSetAttribute(ekf_landmarks_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 cudaSharedmemCarveoutMaxShared) == cudaSuccess;
   if (!ok) { ekf_landmarks_destroy(h); return EKF_ERR_CUDA; }
   *out = h;
   return EKF_OK;
@@ -66,14 +60,13 @@ int ekf_landmarks_detect_dev(ekf_landmarks *h, int32_t n_scans, const float *ran
   if (!h || n_scans < 1 || !ranges_dev || !out_xyr_dev || !out_count_dev || !out_status_dev) return EKF_ERR_INVALID;
   DeviceGuard guard(h->device);
   LmParams p{};
-  p.ranges = ranges_dev; p.n_scans = n_scans; p.n_ranges = h->n_ranges; p.max_out = h->max_out;
-  p.angle_min = angle_min; p.angle_increment = angle_increment; p.thr = cluster_threshold;
+  p.ranges = ranges_dev; p.beam = h->beam_dev; p.n_scans = n_scans; p.n_ranges = h->n_ranges; p.max_out = h->max_out;
+  p.thr = cluster_threshold;
   p.out = out_xyr_dev; p.count = out_count_dev; p.status = out_status_dev;
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
-  const size_t smem = lm_smem_bytes(h->n_ranges);
-  if (h->threads == 128) ekf_landmarks_kernel<128><<<n_scans, 128, smem, st>>>(p);
-  else if (h->threads == 64) ekf_landmarks_kernel<64><<<n_scans, 64, smem, st>>>(p);
-  else ekf_landmarks_kernel<32><<<n_scans, 32, smem, st>>>(p);
+  lm_beam_table_kernel<<<(h->n_ranges + 127) / 128, 128, 0, st>>>(h->beam_dev, h->n_ranges, angle_min, angle_increment);
+  ekf_landmarks_kernel<<<n_scans, kLmThreads, lm_smem_bytes(h->n_ranges), st>>>(p);
+  h->launches++;
   h->launches++;
   return cudaGetLastError() == cudaSuccess ? EKF_OK : EKF_ERR_CUDA;
 }

@@ -1,6 +1,6 @@
 // Landmark extraction, the step right before the EKF hot path: a batch of
 // LaserScans -> clusters -> circle test -> algebraic circle fit -> (c_x, c_y, r) detections, i.e. the
-// sightings `ekf_update_unknown` consumes.  One CTA per scan.
+// sightings `ekf_update_unknown` consumes.  One warp per scan.
 //
 // Replaces, per scan,
 //   nuslam/src/landmarks.cpp:58-106    getClusters: beam -> (x, y) (lidar 0.032 m ahead of the base),
@@ -12,14 +12,21 @@
 //   turtlelib/src/landmark_detection.cpp:50-135  fitCircle: SVD of Z = [z x y 1], Y = V S V^T,
 //                                      Q = Y H^-1 Y, eigenvector of the smallest positive eigenvalue,
 //                                      A = Y^-1 A*   (arma::svd / eig_sym / solve in the reference)
-// The dense factorizations are 4-wide, so each cluster is one thread: a one-sided (Hestenes) Jacobi
-// SVD of Z (accurate for the small singular values the reference's 1e-11 test looks at) and a cyclic
-// Jacobi eigen-solver for the symmetric 4x4 Q.  A cluster's points stay where the scan put them in shared
-// memory (ClusterView maps the cluster's index to the scan's, the wrapped first cluster has two ranges) and
-// the n x 4 matrix Z the SVD rotates in place lives in a shared workspace with one slot per reading - clusters
-// are disjoint sets of readings, so they never collide.  (Per-thread arrays of 39 points went to local
-// memory, 2.2 KB per thread, and every access of the Jacobi loops was an L2 round trip: 9.2 ms per 65,536
-// scans; consecutive clusters are also dealt to different warps so that fewer fits serialise in one.)
+//
+// Shape (round 2; the ncu capture of the first shape - a thread per cluster rotating the n x 4 matrix Z in a
+// shared workspace - showed a latency-bound kernel: 10 warps per SM, 16 % of the issue slots, 16 cycles per
+// instruction, a third of the instructions in the Jacobi loops over the points):
+//   * the beams' (cos, sin) are the same for every scan of a launch: a table made once per call;
+//   * a cluster is still one thread (the factorizations are 4 wide), but Z is never stored: a modified
+//     Gram-Schmidt QR evaluated on the fly (five passes over the cluster's points, each recomputing the point's
+//     row of Z and its projections from px / py) leaves the 4 x 4 triangular factor R in registers, and the
+//     one-sided (Hestenes) Jacobi SVD runs on R - same singular values and right singular vectors as Z, R
+//     accurate to eps * |Z| like the reference's LAPACK path, 100 n instead of 340 n instructions per cluster;
+//   * the inscribed angles of the circle test are summed in one pass (shifted by the first angle), so they
+//     need no workspace either;
+//   * detections go straight to the output in cluster order (ballot + popcount, no staging).
+// Shared memory per scan is then px, py and the gap positions only (18 bytes per reading, 6.5 KB at 360 beams
+// instead of 20 KB), and resident scans per SM are bounded by registers (16 warps), not shared memory (10).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -28,14 +35,14 @@
 
 namespace ekf {
 
-constexpr int kLmThreadsDefault = 32;   // one warp per scan (measured against 64 and 128: see DESIGN.md section 10)
+constexpr int kLmThreads = 32;       // one warp per scan
 constexpr int kLmMaxPts = 39;        // clusters.at(i).size() < 40: landmarks.cpp:122
 constexpr int kLmErrNoGap = 3;       // the reference throws at clusters.at(0): landmarks.cpp:95
 
 struct LmParams {
   const float *ranges;     // [n_scans][n_ranges]
+  const double2 *beam;     // [n_ranges] (cos, sin) of the beam angles of this call (lm_beam_table_kernel)
   int n_scans, n_ranges, max_out;
-  float angle_min, angle_increment;
   double thr;              // distance_clustering_threshold (landmarks.cpp:195)
   double *out;             // [n_scans][max_out][3] (c_x, c_y, r), cluster order
   int *count;              // [n_scans] detections found (may exceed max_out; only max_out are stored)
@@ -43,7 +50,15 @@ struct LmParams {
 };
 
 __host__ __device__ inline size_t lm_smem_bytes(int n_ranges) {
-  return (size_t)n_ranges * (2 * sizeof(double) + 2 * sizeof(int)) + 4 * (size_t)n_ranges * sizeof(double) + 64;
+  return (size_t)n_ranges * (2 * sizeof(double) + sizeof(unsigned short)) + 16;
+}
+
+// landmarks.cpp:66-67: the angle of beam i, the same for every scan of a call
+__global__ void lm_beam_table_kernel(double2 *beam, int n, float angle_min, float angle_increment) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double ang = normalize_angle((double)i * (double)angle_increment) + (double)angle_min;
+  beam[i] = make_double2(cos(ang), sin(ang));
 }
 
 // A cluster's points inside the scan's shared-memory arrays: index i of the cluster is reading start + i for
@@ -53,9 +68,15 @@ struct ClusterView {
   __device__ __forceinline__ int at(int i) const { return i < len ? start + i : tail0 + (i - len); }
 };
 
-// one-sided Jacobi SVD of Z (n x 4; column c of point i at zw[c * ld + cv.at(i)]): on exit the columns are U S,
-// v holds V
-__device__ inline void svd4(double *zw, int ld, const ClusterView &cv, int n, double v[4][4], double s[4]) {
+// Jacobi rotation that zeroes the (p, q) coupling: (c, s) from zeta = (beta - alpha) / (2 gamma)
+__device__ __forceinline__ void jacobi_cs(double zeta, double &c, double &sn) {
+  const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+  c = 1.0 / sqrt(1.0 + t * t);
+  sn = c * t;
+}
+
+// one-sided Jacobi SVD of a 4 x 4 matrix held by columns (z[c][row]): on exit the columns are U S, v holds V
+__device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[4]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -66,29 +87,26 @@ __device__ inline void svd4(double *zw, int ld, const ClusterView &cv, int n, do
     for (int p = 0; p < 3; ++p)
 #pragma unroll
       for (int q = p + 1; q < 4; ++q) {
-        double *zp = zw + p * ld, *zq = zw + q * ld;
         double al = 0.0, be = 0.0, ga = 0.0;
-        for (int i = 0; i < n; ++i) {
-          const int o = cv.at(i);
-          const double a = zp[o], b = zq[o];
-          al += a * a; be += b * b; ga += a * b;
-        }
-        if (ga == 0.0) continue;
-        const double rel = fabs(ga) / sqrt(al * be);
-        if (rel > off) off = rel;
-        if (rel < 1.0e-16) continue;
-        const double zeta = (be - al) / (2.0 * ga);
-        const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-        const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
-        for (int i = 0; i < n; ++i) {
-          const int o = cv.at(i);
-          const double a = zp[o], b = zq[o];
-          zp[o] = c * a - sn * b; zq[o] = sn * a + c * b;
-        }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const double a = v[i][p], b = v[i][q];
-          v[i][p] = c * a - sn * b; v[i][q] = sn * a + c * b;
+        for (int i = 0; i < 4; ++i) { al += z[p][i] * z[p][i]; be += z[q][i] * z[q][i]; ga += z[p][i] * z[q][i]; }
+        if (ga != 0.0) {
+          const double rel = fabs(ga) / sqrt(al * be);
+          if (rel > off) off = rel;
+          if (rel >= 1.0e-16) {
+            double c, sn;
+            jacobi_cs((be - al) / (2.0 * ga), c, sn);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const double a = z[p][i], b = z[q][i];
+              z[p][i] = c * a - sn * b; z[q][i] = sn * a + c * b;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const double a = v[i][p], b = v[i][q];
+              v[i][p] = c * a - sn * b; v[i][q] = sn * a + c * b;
+            }
+          }
         }
       }
     if (off < 1.0e-15) break;
@@ -96,7 +114,8 @@ __device__ inline void svd4(double *zw, int ld, const ClusterView &cv, int n, do
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     double a = 0.0;
-    for (int i = 0; i < n; ++i) { const double e = zw[j * ld + cv.at(i)]; a += e * e; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a += z[j][i] * z[j][i];
     s[j] = sqrt(a);
   }
 }
@@ -143,23 +162,62 @@ __device__ inline void eig4(double a[4][4], double e[4][4]) {
   }
 }
 
-// turtlelib/src/landmark_detection.cpp:50-135 on the n points of a cluster; zw = Z workspace (4 columns of ld)
-__device__ inline void fit_circle(const double *px, const double *py, double *zw, int ld, const ClusterView &cv, int n,
-                                  double &cx, double &cy, double &R) {
+// turtlelib/src/landmark_detection.cpp:50-135 on the n points of a cluster.  Z = [z x y 1] (centred points,
+// z = x^2 + y^2) is reduced to its triangular factor R by modified Gram-Schmidt without being stored: pass c
+// recomputes, per point, the row of Z and what the earlier columns left of it, and accumulates column c's norm
+// and its products with the later columns.  The SVD of R gives Z's singular values and V.
+__device__ inline void fit_circle(const double *px, const double *py, const ClusterView &cv, int n, double &cx,
+                                  double &cy, double &R) {
   double mx = 0.0, my = 0.0;
   for (int i = 0; i < n; ++i) { const int o = cv.at(i); mx += px[o]; my += py[o]; }
   mx /= n; my /= n;
-  double zm = 0.0;
+  double s00 = 0.0, s01 = 0.0, s02 = 0.0, s03 = 0.0;
   for (int i = 0; i < n; ++i) {
     const int o = cv.at(i);
     const double xi = px[o] - mx, yi = py[o] - my;
     const double z0 = xi * xi + yi * yi;
-    zw[o] = z0; zw[ld + o] = xi; zw[2 * ld + o] = yi; zw[3 * ld + o] = 1.0;
-    zm += z0;
+    s00 += z0 * z0; s01 += z0 * xi; s02 += z0 * yi; s03 += z0;
   }
-  zm /= n;
+  const double zm = s03 / n;                                   // mean of z (landmark_detection.cpp:72-77)
+  const double r00 = sqrt(s00), i0 = r00 > 0.0 ? 1.0 / r00 : 0.0;
+  const double r01 = s01 * i0, r02 = s02 * i0, r03 = s03 * i0;
+  double s11 = 0.0, s12 = 0.0, s13 = 0.0;
+  for (int i = 0; i < n; ++i) {
+    const int o = cv.at(i);
+    const double xi = px[o] - mx, yi = py[o] - my;
+    const double q0 = (xi * xi + yi * yi) * i0;
+    const double a1 = xi - r01 * q0, a2 = yi - r02 * q0, a3 = 1.0 - r03 * q0;
+    s11 += a1 * a1; s12 += a1 * a2; s13 += a1 * a3;
+  }
+  const double r11 = sqrt(s11), i1 = r11 > 0.0 ? 1.0 / r11 : 0.0;
+  const double r12 = s12 * i1, r13 = s13 * i1;
+  double s22 = 0.0, s23 = 0.0;
+  for (int i = 0; i < n; ++i) {
+    const int o = cv.at(i);
+    const double xi = px[o] - mx, yi = py[o] - my;
+    const double q0 = (xi * xi + yi * yi) * i0;
+    const double a1 = xi - r01 * q0, a2 = yi - r02 * q0, a3 = 1.0 - r03 * q0;
+    const double q1 = a1 * i1;
+    const double b2 = a2 - r12 * q1, b3 = a3 - r13 * q1;
+    s22 += b2 * b2; s23 += b2 * b3;
+  }
+  const double r22 = sqrt(s22), i2 = r22 > 0.0 ? 1.0 / r22 : 0.0;
+  const double r23 = s23 * i2;
+  double s33 = 0.0;
+  for (int i = 0; i < n; ++i) {
+    const int o = cv.at(i);
+    const double xi = px[o] - mx, yi = py[o] - my;
+    const double q0 = (xi * xi + yi * yi) * i0;
+    const double a1 = xi - r01 * q0, a2 = yi - r02 * q0, a3 = 1.0 - r03 * q0;
+    const double q1 = a1 * i1;
+    const double b2 = a2 - r12 * q1, b3 = a3 - r13 * q1;
+    const double c3 = b3 - r23 * (b2 * i2);
+    s33 += c3 * c3;
+  }
+  const double r33 = sqrt(s33);
+  double rc[4][4] = {{r00, 0.0, 0.0, 0.0}, {r01, r11, 0.0, 0.0}, {r02, r12, r22, 0.0}, {r03, r13, r23, r33}};   // columns of R
   double v[4][4], s[4];
-  svd4(zw, ld, cv, n, v, s);
+  svd4x4(rc, v, s);
   int imin = 0;
 #pragma unroll
   for (int j = 1; j < 4; ++j) if (s[j] < s[imin]) imin = j;
@@ -246,132 +304,105 @@ __device__ inline void fit_circle(const double *px, const double *py, double *zw
   cx = a + mx; cy = b + my;
 }
 
-// turtlelib/src/landmark_detection.cpp:5-48; ang = workspace of one double per reading (the cluster's own slots)
-__device__ inline bool check_circle(const double *px, const double *py, double *ang, const ClusterView &cv, int n) {
+// turtlelib/src/landmark_detection.cpp:5-48.  Mean and N-1 standard deviation of the inscribed angles in one pass
+// (sums of the angles' differences from the first one: no cancellation to speak of, no workspace)
+__device__ inline bool check_circle(const double *px, const double *py, const ClusterView &cv, int n) {
   const int o0 = cv.at(0), oe = cv.at(n - 1);
   const double sx = px[o0], sy = py[o0], ex = px[oe], ey = py[oe];
   const double c = sqrt(sq_sum(sx - ex, sy - ey));
-  double sum = 0.0;
+  double first = 0.0, sd = 0.0, sd2 = 0.0;
   for (int j = 1; j < n - 1; ++j) {
     const int o = cv.at(j);
     const double a = sqrt(sq_sum(sx - px[o], sy - py[o])), b = sqrt(sq_sum(ex - px[o], ey - py[o]));
     const double an = acos((c * c - a * a - b * b) / (-2.0 * a * b));
-    ang[o] = an;
-    sum += an;
+    if (j == 1) first = an;
+    const double d = an - first;
+    sd += d; sd2 += d * d;
   }
   const int k = n - 2;
-  const double mn = sum / k;
-  double var = 0.0;
-  for (int j = 1; j < n - 1; ++j) { const double d = ang[cv.at(j)] - mn; var += d * d; }
-  const double stdev = k > 1 ? sqrt(var / (k - 1)) : 0.0;   // arma::stddev: N-1 normalisation
+  const double mn = first + sd / k;
+  const double var = k > 1 ? (sd2 - sd * sd / k) / (k - 1) : 0.0;
+  const double stdev = sqrt(var > 0.0 ? var : 0.0);          // arma::stddev: N-1 normalisation
   return stdev < 0.2 && 1.3 < mn && mn < 2.6;
 }
 
-// block-wide exclusive prefix sum of one int per thread (kLmThreads threads); returns the total too
-template <int kLmThreads>
-__device__ inline int block_exscan(int v, int *s_warp, int &total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int inc = v;
+__global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmParams p) {
+  extern __shared__ __align__(16) unsigned char lm_smem[];
+  const int n = p.n_ranges;
+  double *px = reinterpret_cast<double *>(lm_smem);
+  double *py = px + n;
+  unsigned short *gpos = reinterpret_cast<unsigned short *>(py + n);   // gap positions, in order (n <= 4096)
+  const int scan = blockIdx.x, lane = threadIdx.x;
+  if (scan >= p.n_scans) return;
+  const float *rg = p.ranges + (size_t)scan * n;
+
+  // landmarks.cpp:66-69
+  for (int i = lane; i < n; i += kLmThreads) {
+    const double r = (double)rg[i];
+    const double2 cs = p.beam[i];
+    px[i] = r * cs.x - 0.032;
+    py[i] = r * cs.y;
+  }
+  __syncwarp();
+
+  // gaps (landmarks.cpp:75-86), ordered positions by a warp scan over contiguous per-lane slices
+  const int per = (n + kLmThreads - 1) / kLmThreads;
+  const int i0 = lane * per, i1 = min(n, i0 + per);
+  auto is_gap = [&](int i) { return sqrt(sq_sum(px[i] - px[i - 1], py[i] - py[i - 1])) > p.thr; };
+  unsigned long long gmask = 0;                          // the slice's gaps when it is at most 64 readings long
+  int local = 0;
+  for (int i = max(i0, 1); i < i1; ++i)
+    if (is_gap(i)) { ++local; if (per <= 64) gmask |= 1ULL << (i - i0); }
+  int inc = local;
 #pragma unroll
   for (int off = 1; off < 32; off <<= 1) {
     const int o = __shfl_up_sync(0xffffffffu, inc, off);
     if (lane >= off) inc += o;
   }
-  if (lane == 31) s_warp[warp] = inc;
-  __syncthreads();
-  int base = 0, tot = 0;
-  for (int w = 0; w < kLmThreads / 32; ++w) { if (w < warp) base += s_warp[w]; tot += s_warp[w]; }
-  __syncthreads();
-  total = tot;
-  return base + inc - v;
-}
-
-template <int kLmThreads>
-__global__ void __launch_bounds__(kLmThreads) ekf_landmarks_kernel(const LmParams p) {
-  extern __shared__ __align__(16) unsigned char lm_smem[];
-  const int n = p.n_ranges;
-  double *px = reinterpret_cast<double *>(lm_smem);
-  double *py = px + n;
-  double *res = py + n;                 // [4][n]: workspace of the fits (Z columns / inscribed angles), then per cluster
-                                        // (cx, cy, r, keep) at the cluster's first reading
-  int *gpos = reinterpret_cast<int *>(res + 4 * (size_t)n);   // gap positions, in order
-  int *s_warp = gpos + n;               // scan scratch (needs 4) - the tail of the buffer
-  const int scan = blockIdx.x, tid = threadIdx.x;
-  if (scan >= p.n_scans) return;
-  const float *rg = p.ranges + (size_t)scan * n;
-
-  // landmarks.cpp:66-69
-  for (int i = tid; i < n; i += kLmThreads) {
-    const double ang = normalize_angle((double)i * (double)p.angle_increment) + (double)p.angle_min;
-    const double r = (double)rg[i];
-    px[i] = r * cos(ang) - 0.032;
-    py[i] = r * sin(ang);
-  }
-  __syncthreads();
-
-  // gaps (landmarks.cpp:75-86), ordered positions by a block scan over contiguous per-thread slices
-  const int per = (n + kLmThreads - 1) / kLmThreads;
-  const int i0 = tid * per, i1 = min(n, i0 + per);
-  int local = 0;
+  const int G = __shfl_sync(0xffffffffu, inc, 31);
+  int rank = inc - local;
   for (int i = max(i0, 1); i < i1; ++i)
-    if (sqrt(sq_sum(px[i] - px[i - 1], py[i] - py[i - 1])) > p.thr) ++local;
-  int G = 0;
-  int rank = block_exscan<kLmThreads>(local, s_warp, G);
-  for (int i = max(i0, 1); i < i1; ++i)
-    if (sqrt(sq_sum(px[i] - px[i - 1], py[i] - py[i - 1])) > p.thr) gpos[rank++] = i;
-  __syncthreads();
+    if (per <= 64 ? (int)((gmask >> (i - i0)) & 1ULL) : (int)is_gap(i)) gpos[rank++] = (unsigned short)i;
+  __syncwarp();
 
   if (G == 0) {                         // clusters.at(0) throws in the reference (landmarks.cpp:95)
-    if (tid == 0) { p.count[scan] = 0; p.status[scan] = kLmErrNoGap; }
+    if (lane == 0) { p.count[scan] = 0; p.status[scan] = kLmErrNoGap; }
     return;
   }
   const bool wrap = sqrt(sq_sum(px[0] - px[n - 1], py[0] - py[n - 1])) <= p.thr;   // landmarks.cpp:93-103
   const int n_clusters = wrap ? G : G + 1;
 
-  // one thread per cluster: size filter, circle test, fit, final filter (landmarks.cpp:117-149).  Cluster k goes to
-  // lane k / 4 of warp k % 4; its result (cx, cy, r, keep) is left in the four workspace columns at the cluster's
-  // first reading (an empty cluster - two gaps in a row, or a gap at the last reading - has no slot and is not kept)
-  for (int k = (tid & 31) * (kLmThreads / 32) + (tid >> 5); k < n_clusters; k += kLmThreads) {
-    ClusterView cv;
-    cv.start = (k == 0) ? 0 : gpos[k - 1] + 1;
-    const int end = (k < G) ? gpos[k] : n;                     // exclusive
-    cv.len = end - cv.start;
-    cv.tail0 = gpos[G - 1] + 1;
-    const int tail = (k == 0 && wrap) ? n - cv.tail0 : 0;
-    const int total = cv.len + tail;
-    double keep = 0.0, cx = 0.0, cy = 0.0, R = 0.0;
-    if (total > 3 && total <= kLmMaxPts) {
-      if (check_circle(px, py, res, cv, total)) {
-        fit_circle(px, py, res, n, cv, total, cx, cy, R);
-        if (R < 0.2 && sqrt(sq_sum(cx, cy)) < 2.0) keep = 1.0;
+  // one lane per cluster: size filter, circle test, fit, final filter (landmarks.cpp:117-149); detections leave in
+  // cluster order (marker id = running index, :137-148)
+  int written = 0;
+  for (int base = 0; base < n_clusters; base += kLmThreads) {
+    const int k = base + lane;
+    bool keep = false;
+    double cx = 0.0, cy = 0.0, R = 0.0;
+    if (k < n_clusters) {
+      ClusterView cv;
+      cv.start = (k == 0) ? 0 : (int)gpos[k - 1] + 1;
+      const int end = (k < G) ? (int)gpos[k] : n;                // exclusive
+      cv.len = end - cv.start;
+      cv.tail0 = (int)gpos[G - 1] + 1;
+      const int tail = (k == 0 && wrap) ? n - cv.tail0 : 0;
+      const int total = cv.len + tail;
+      if (total > 3 && total <= kLmMaxPts) {
+        if (check_circle(px, py, cv, total)) {
+          fit_circle(px, py, cv, total, cx, cy, R);
+          keep = R < 0.2 && sqrt(sq_sum(cx, cy)) < 2.0;
+        }
       }
     }
-    if (cv.len > 0) { res[cv.start] = cx; res[n + cv.start] = cy; res[2 * n + cv.start] = R; res[3 * n + cv.start] = keep; }
-  }
-  __syncthreads();
-  // ordered compaction: detections come out in cluster order (marker id = running index, :137-148)
-  auto slot_of = [&](int k) {                                  // the cluster's first reading, or -1 for an empty cluster
-    const int start = (k == 0) ? 0 : gpos[k - 1] + 1;
-    const int end = (k < G) ? gpos[k] : n;
-    return end > start ? start : -1;
-  };
-  int keep_local = 0;
-  const int perc = (n_clusters + kLmThreads - 1) / kLmThreads;
-  const int c0 = tid * perc, c1 = min(n_clusters, c0 + perc);
-  for (int k = c0; k < c1; ++k) { const int o = slot_of(k); keep_local += (o >= 0 && res[3 * n + o] != 0.0); }
-  int total_keep = 0;
-  int orank = block_exscan<kLmThreads>(keep_local, s_warp, total_keep);
-  for (int k = c0; k < c1; ++k) {
-    const int o = slot_of(k);
-    if (o >= 0 && res[3 * n + o] != 0.0) {
-      if (orank < p.max_out) {
-        double *d = p.out + ((size_t)scan * p.max_out + orank) * 3;
-        d[0] = res[o]; d[1] = res[n + o]; d[2] = res[2 * n + o];
-      }
-      ++orank;
+    const unsigned km = __ballot_sync(0xffffffffu, keep);
+    const int orank = written + __popc(km & ((1u << lane) - 1u));
+    if (keep && orank < p.max_out) {
+      double *d = p.out + ((size_t)scan * p.max_out + orank) * 3;
+      d[0] = cx; d[1] = cy; d[2] = R;
     }
+    written += __popc(km);
   }
-  if (tid == 0) { p.count[scan] = total_keep; p.status[scan] = 0; }
+  if (lane == 0) { p.count[scan] = written; p.status[scan] = 0; }
 }
 
 }  // namespace ekf
