@@ -35,6 +35,14 @@ __host__ __device__ inline T2 t2_mul(const T2 a, const T2 b) {     // se2d.cpp:6
   return T2{c * b.x - s * b.y + a.x, s * b.x + c * b.y + a.y, a.rot + b.rot};
 }
 
+// the same with cos / sin of a.rot supplied by the caller (the lidar evaluates each angle's pair once)
+__host__ __device__ inline T2 t2_inv_cs(const T2 a, double c, double s) {
+  return T2{-a.x * c - a.y * s, -a.y * c + a.x * s, -a.rot};
+}
+__host__ __device__ inline T2 t2_mul_cs(const T2 a, double c, double s, const T2 b) {
+  return T2{c * b.x - s * b.y + a.x, s * b.x + c * b.y + a.y, a.rot + b.rot};
+}
+
 // splitmix64 -> two uniforms -> Box-Muller: one standard normal per (seed, stream, index)
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
   z += 0x9E3779B97F4A7C15ull;
@@ -87,10 +95,16 @@ __global__ void __launch_bounds__(128) nusim_lidar_kernel(const double *poses, i
   if (e >= (int64_t)n_robots * kLidarBeams) return;
   const int r = (int)(e / kLidarBeams), i = (int)(e % kLidarBeams);
   const T2 Twt{poses[3 * r + 1], poses[3 * r + 2], poses[3 * r]};
-  const T2 Ttl = t2_mul(T2{-0.032, 0.0, 0.0}, T2{0.0, 0.0, (double)i * 2.0 * 3.14159265358979323846 / 360.0});  // :577-580
-  const T2 Twl = t2_mul(Twt, Ttl);                                                      // :581
-  const T2 p2 = t2_mul(Twl, T2{1.0, 0.0, 0.0});                                         // :585
-  const T2 Tlw = t2_inv(Twl);
+  // Four transforms of the reference, two angles: cos / sin of the robot's heading and of the beam's world heading are
+  // evaluated once each; the inverse transform's are (c, -s) - cos is even and sin odd bit for bit, so this is what
+  // se2d.cpp:57-74 computes with its own calls
+  const T2 Ttl = t2_mul_cs(T2{-0.032, 0.0, 0.0}, 1.0, 0.0, T2{0.0, 0.0, (double)i * 2.0 * 3.14159265358979323846 / 360.0});  // :577-580
+  double c_r, s_r, c_b, s_b;
+  sincos(Twt.rot, &s_r, &c_r);
+  const T2 Twl = t2_mul_cs(Twt, c_r, s_r, Ttl);                                         // :581
+  sincos(Twl.rot, &s_b, &c_b);
+  const T2 p2 = t2_mul_cs(Twl, c_b, s_b, T2{1.0, 0.0, 0.0});                            // :585
+  const T2 Tlw = t2_inv_cs(Twl, c_b, s_b);
   const double x1 = Twl.x, y1 = Twl.y, x2 = p2.x, y2 = p2.y;
   // beam direction: normalize(p2 - p1), :604-606
   const double ddx = x2 - x1, ddy = y2 - y1;
@@ -100,7 +114,7 @@ __global__ void __launch_bounds__(128) nusim_lidar_kernel(const double *poses, i
   double closest = max_range;                                                           // :588
   for (int j = 0; j < world.n_obstacles; ++j) {
     const double mx = s_obs[3 * j], my = s_obs[3 * j + 1], rad = s_obs[3 * j + 2];
-    const T2 Tlm = t2_mul(Tlw, T2{mx, my, 0.0});                                        // :596
+    const T2 Tlm = t2_mul_cs(Tlw, c_b, -s_b, T2{mx, my, 0.0});                          // :596
     if (Tlm.x >= 0) {                                                                   // :598
       const double ux = mx - x1, uy = my - y1;                                          // :600-601
       const double dt = ux * rx + uy * ry;
@@ -126,7 +140,7 @@ __global__ void __launch_bounds__(128) nusim_lidar_kernel(const double *poses, i
       const double num_y = (x1 * y2 - y1 * x2) * (y3 - y4) - (y1 - y2) * (x3 * y4 - y3 * x4);
       if (denom != 0.0) {                                                               // :682
         const double px = num_x / denom, py = num_y / denom;
-        const T2 Tl = t2_mul(Tlw, T2{px, py, 0.0});                                     // :685-686
+        const T2 Tl = t2_mul_cs(Tlw, c_b, -s_b, T2{px, py, 0.0});                       // :685-686
         if (Tl.x > 0) {                                                                 // :687
           const double dist = sqrt((x1 - px) * (x1 - px) + (y1 - py) * (y1 - py));      // :688-690
           if (dist < closest) closest = dist;                                           // :691-693
