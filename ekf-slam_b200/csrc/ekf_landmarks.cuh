@@ -68,12 +68,18 @@ struct ClusterView {
   __device__ __forceinline__ int at(int i) const { return i < len ? start + i : tail0 + (i - len); }
 };
 
-// Jacobi rotation that zeroes the (p, q) coupling: (c, s) from zeta = (beta - alpha) / (2 gamma)
-__device__ __forceinline__ void jacobi_cs(double zeta, double &c, double &sn) {
+// Jacobi rotation that zeroes the (p, q) coupling: (c, s) from zeta = (beta - alpha) / (2 gamma).  Deliberately ONE
+// copy in the kernel (two divisions and two square roots in fp64 are ~150 instructions; inlined into the twelve unrolled
+// rotations of svd4x4 and eig4 the kernel was 109 KB of code and its warps - sixteen per SM, each somewhere else in it -
+// waited for instruction fetch 6.5 cycles per issued instruction, `stalled_no_instruction` in the ncu capture)
+__device__ __noinline__ double2 jacobi_cs(double num, double den) {
+  const double zeta = num / den;
   const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-  c = 1.0 / sqrt(1.0 + t * t);
-  sn = c * t;
+  const double c = 1.0 / sqrt(1.0 + t * t);
+  return make_double2(c, c * t);
 }
+// |gamma| / sqrt(alpha beta): the cosine of the angle between two columns (one copy, as above)
+__device__ __noinline__ double column_cosine(double al, double be, double ga) { return fabs(ga) / sqrt(al * be); }
 
 // one-sided Jacobi SVD of a 4 x 4 matrix held by columns (z[c][row]): on exit the columns are U S, v holds V
 __device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[4]) {
@@ -91,11 +97,11 @@ __device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[
 #pragma unroll
         for (int i = 0; i < 4; ++i) { al += z[p][i] * z[p][i]; be += z[q][i] * z[q][i]; ga += z[p][i] * z[q][i]; }
         if (ga != 0.0) {
-          const double rel = fabs(ga) / sqrt(al * be);
+          const double rel = column_cosine(al, be, ga);
           if (rel > off) off = rel;
           if (rel >= 1.0e-16) {
-            double c, sn;
-            jacobi_cs((be - al) / (2.0 * ga), c, sn);
+            const double2 cs = jacobi_cs(be - al, 2.0 * ga);
+            const double c = cs.x, sn = cs.y;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               const double a = z[p][i], b = z[q][i];
@@ -140,9 +146,8 @@ __device__ inline void eig4(double a[4][4], double e[4][4]) {
 #pragma unroll
       for (int q = p + 1; q < 4; ++q) {
         if (a[p][q] == 0.0) continue;
-        const double theta = (a[q][q] - a[p][p]) / (2.0 * a[p][q]);
-        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(1.0 + theta * theta));
-        const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+        const double2 cs = jacobi_cs(a[q][q] - a[p][p], 2.0 * a[p][q]);
+        const double c = cs.x, sn = cs.y;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {            // A <- A J
           const double x = a[k][p], y = a[k][q];
@@ -169,9 +174,11 @@ __device__ inline void eig4(double a[4][4], double e[4][4]) {
 __device__ inline void fit_circle(const double *px, const double *py, const ClusterView &cv, int n, double &cx,
                                   double &cy, double &R) {
   double mx = 0.0, my = 0.0;
+#pragma unroll 1
   for (int i = 0; i < n; ++i) { const int o = cv.at(i); mx += px[o]; my += py[o]; }
   mx /= n; my /= n;
   double s00 = 0.0, s01 = 0.0, s02 = 0.0, s03 = 0.0;
+#pragma unroll 1
   for (int i = 0; i < n; ++i) {
     const int o = cv.at(i);
     const double xi = px[o] - mx, yi = py[o] - my;
@@ -182,6 +189,7 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
   const double r00 = sqrt(s00), i0 = r00 > 0.0 ? 1.0 / r00 : 0.0;
   const double r01 = s01 * i0, r02 = s02 * i0, r03 = s03 * i0;
   double s11 = 0.0, s12 = 0.0, s13 = 0.0;
+#pragma unroll 1
   for (int i = 0; i < n; ++i) {
     const int o = cv.at(i);
     const double xi = px[o] - mx, yi = py[o] - my;
@@ -192,6 +200,7 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
   const double r11 = sqrt(s11), i1 = r11 > 0.0 ? 1.0 / r11 : 0.0;
   const double r12 = s12 * i1, r13 = s13 * i1;
   double s22 = 0.0, s23 = 0.0;
+#pragma unroll 1
   for (int i = 0; i < n; ++i) {
     const int o = cv.at(i);
     const double xi = px[o] - mx, yi = py[o] - my;
@@ -204,6 +213,7 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
   const double r22 = sqrt(s22), i2 = r22 > 0.0 ? 1.0 / r22 : 0.0;
   const double r23 = s23 * i2;
   double s33 = 0.0;
+#pragma unroll 1
   for (int i = 0; i < n; ++i) {
     const int o = cv.at(i);
     const double xi = px[o] - mx, yi = py[o] - my;
@@ -311,6 +321,7 @@ __device__ inline bool check_circle(const double *px, const double *py, const Cl
   const double sx = px[o0], sy = py[o0], ex = px[oe], ey = py[oe];
   const double c = sqrt(sq_sum(sx - ex, sy - ey));
   double first = 0.0, sd = 0.0, sd2 = 0.0;
+#pragma unroll 1
   for (int j = 1; j < n - 1; ++j) {
     const int o = cv.at(j);
     const double a = sqrt(sq_sum(sx - px[o], sy - py[o])), b = sqrt(sq_sum(ex - px[o], ey - py[o]));
@@ -326,7 +337,8 @@ __device__ inline bool check_circle(const double *px, const double *py, const Cl
   return stdev < 0.2 && 1.3 < mn && mn < 2.6;
 }
 
-__global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmParams p) {
+template <int MINB>
+__global__ void __launch_bounds__(kLmThreads, MINB) ekf_landmarks_kernel(const LmParams p) {
   extern __shared__ __align__(16) unsigned char lm_smem[];
   const int n = p.n_ranges;
   double *px = reinterpret_cast<double *>(lm_smem);
@@ -351,6 +363,7 @@ __global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmP
   auto is_gap = [&](int i) { return sqrt(sq_sum(px[i] - px[i - 1], py[i] - py[i - 1])) > p.thr; };
   unsigned long long gmask = 0;                          // the slice's gaps when it is at most 64 readings long
   int local = 0;
+#pragma unroll 1
   for (int i = max(i0, 1); i < i1; ++i)
     if (is_gap(i)) { ++local; if (per <= 64) gmask |= 1ULL << (i - i0); }
   int inc = local;
@@ -361,6 +374,7 @@ __global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmP
   }
   const int G = __shfl_sync(0xffffffffu, inc, 31);
   int rank = inc - local;
+#pragma unroll 1
   for (int i = max(i0, 1); i < i1; ++i)
     if (per <= 64 ? (int)((gmask >> (i - i0)) & 1ULL) : (int)is_gap(i)) gpos[rank++] = (unsigned short)i;
   __syncwarp();
