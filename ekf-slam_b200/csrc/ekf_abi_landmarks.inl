@@ -5,22 +5,11 @@ struct ekf_landmarks {
   int max_scans = 0, n_ranges = 0, max_out = 0;
   float *ranges_dev = nullptr;
   double2 *beam_dev = nullptr;   // (cos, sin) of the beam angles of the current call
-  int minb = 16;                 // resident scans per SM the kernel's register allocation is sized for
   double *out_dev = nullptr;
   int *count_dev = nullptr, *status_dev = nullptr;
   cudaStream_t stream = nullptr;
   int64_t launches = 0;
 };
-
-namespace {
-template <int MINB> bool lm_set_attributes_of() {
-  return cudaFuncSetAttribute(ekf_landmarks_kernel<MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)lm_smem_bytes(4096)) == cudaSuccess &&
-         cudaFuncSetAttribute(ekf_landmarks_kernel<MINB>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                              cudaSharedmemCarveoutMaxShared) == cudaSuccess;
-}
-bool lm_set_attributes() { return lm_set_attributes_of<16>() && lm_set_attributes_of<20>() && lm_set_attributes_of<24>(); }
-}  // namespace
 
 extern "C" {
 
@@ -56,11 +45,10 @@ int ekf_landmarks_create(int32_t max_scans, int32_t n_ranges, int32_t max_out, i
             cudaMalloc(&h->count_dev, (size_t)max_scans * sizeof(int)) == cudaSuccess &&
             cudaMalloc(&h->status_dev, (size_t)max_scans * sizeof(int)) == cudaSuccess &&
             cudaMalloc(&h->beam_dev, (size_t)n_ranges * sizeof(double2)) == cudaSuccess &&
-            lm_set_attributes();
-  if (const char *e = getenv("EKF_LM_MINB")) {              // development override: resident scans per SM to size for
-    const int v = atoi(e);
-    if (v == 16 || v == 20 || v == 24) h->minb = v;
-  }
+            cudaFuncSetAttribute(ekf_landmarks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)lm_smem_bytes(4096)) == cudaSuccess &&
+            cudaFuncSetAttribute(ekf_landmarks_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 cudaSharedmemCarveoutMaxShared) == cudaSuccess;
   if (!ok) { ekf_landmarks_destroy(h); return EKF_ERR_CUDA; }
   *out = h;
   return EKF_OK;
@@ -77,10 +65,7 @@ int ekf_landmarks_detect_dev(ekf_landmarks *h, int32_t n_scans, const float *ran
   p.out = out_xyr_dev; p.count = out_count_dev; p.status = out_status_dev;
   cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
   lm_beam_table_kernel<<<(h->n_ranges + 127) / 128, 128, 0, st>>>(h->beam_dev, h->n_ranges, angle_min, angle_increment);
-  const size_t smem = lm_smem_bytes(h->n_ranges);
-  if (h->minb == 24) ekf_landmarks_kernel<24><<<n_scans, kLmThreads, smem, st>>>(p);
-  else if (h->minb == 20) ekf_landmarks_kernel<20><<<n_scans, kLmThreads, smem, st>>>(p);
-  else ekf_landmarks_kernel<16><<<n_scans, kLmThreads, smem, st>>>(p);
+  ekf_landmarks_kernel<<<n_scans, kLmThreads, lm_smem_bytes(h->n_ranges), st>>>(p);
   h->launches++;
   h->launches++;
   return cudaGetLastError() == cudaSuccess ? EKF_OK : EKF_ERR_CUDA;

@@ -337,8 +337,8 @@ __device__ inline bool check_circle(const double *px, const double *py, const Cl
   return stdev < 0.2 && 1.3 < mn && mn < 2.6;
 }
 
-template <int MINB>
-__global__ void __launch_bounds__(kLmThreads, MINB) ekf_landmarks_kernel(const LmParams p) {
+// (16 resident scans per SM: 128 registers; sized for 20 or 24 it spills and is no faster - measured)
+__global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmParams p) {
   extern __shared__ __align__(16) unsigned char lm_smem[];
   const int n = p.n_ranges;
   double *px = reinterpret_cast<double *>(lm_smem);
