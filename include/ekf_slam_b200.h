@@ -273,10 +273,13 @@ int ekf_batch_step_bytes(ekf_batch *b, int32_t m, int64_t *bytes);
  * A batch of LaserScans (float ranges, n_ranges beams each, as in sensor_msgs/LaserScan) ->
  * per scan the circle detections (c_x, c_y, r) in the lidar-corrected robot frame, in cluster order:
  * what nuslam's `landmarks` node publishes on green/detected_obstacles (nuslam/src/landmarks.cpp:58-156
- * with turtlelib checkCircle / fitCircle, turtlelib/src/landmark_detection.cpp:5-135).  One CTA per scan.
+ * with turtlelib checkCircle / fitCircle, turtlelib/src/landmark_detection.cpp:5-135).  One warp per scan.
  * out_xyr[n_scans][max_out][3]; out_count[s] = detections of scan s (only the first max_out are stored);
  * out_status[s] = 0, or EKF_ERR_EMPTY_SCAN when the scan has no range discontinuity at all (the
- * reference throws at clusters.at(0), landmarks.cpp:95).  cluster_threshold = 0.2 in the reference. */
+ * reference throws at clusters.at(0), landmarks.cpp:95).  cluster_threshold = 0.2 in the reference.
+ * A call first writes the handle's table of beam directions for its (angle_min, angle_increment), then runs the
+ * scans, both on the call's stream: calls on ONE handle are stream-ordered like every other handle here (one caller
+ * thread, slam.cpp:680-686); two calls in flight on different streams need two handles. */
 int ekf_landmarks_create(int32_t max_scans, int32_t n_ranges, int32_t max_out, int32_t device, ekf_landmarks **out);
 int ekf_landmarks_destroy(ekf_landmarks *h);
 int ekf_landmarks_detect(ekf_landmarks *h, int32_t n_scans, const float *ranges, float angle_min,
