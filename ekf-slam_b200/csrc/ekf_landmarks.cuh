@@ -78,8 +78,6 @@ __device__ __noinline__ double2 jacobi_cs(double num, double den) {
   const double c = 1.0 / sqrt(1.0 + t * t);
   return make_double2(c, c * t);
 }
-// |gamma| / sqrt(alpha beta): the cosine of the angle between two columns (one copy, as above)
-__device__ __noinline__ double column_cosine(double al, double be, double ga) { return fabs(ga) / sqrt(al * be); }
 
 // one-sided Jacobi SVD of a 4 x 4 matrix held by columns (z[c][row]): on exit the columns are U S, v holds V
 __device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[4]) {
@@ -87,8 +85,10 @@ __device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) v[i][j] = (i == j) ? 1.0 : 0.0;
+  // the cosine of the angle between two columns, |gamma| / sqrt(alpha beta), is compared in squared form (no square
+  // root, no division): rotate while it is >= 1e-16, done when every pair of a sweep was below 1e-15
   for (int sweep = 0; sweep < 30; ++sweep) {
-    double off = 0.0;
+    bool done = true;
 #pragma unroll
     for (int p = 0; p < 3; ++p)
 #pragma unroll
@@ -97,9 +97,9 @@ __device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[
 #pragma unroll
         for (int i = 0; i < 4; ++i) { al += z[p][i] * z[p][i]; be += z[q][i] * z[q][i]; ga += z[p][i] * z[q][i]; }
         if (ga != 0.0) {
-          const double rel = column_cosine(al, be, ga);
-          if (rel > off) off = rel;
-          if (rel >= 1.0e-16) {
+          const double g2 = ga * ga, ab = al * be;
+          if (!(g2 < 1.0e-30 * ab)) done = false;
+          if (g2 >= 1.0e-32 * ab) {
             const double2 cs = jacobi_cs(be - al, 2.0 * ga);
             const double c = cs.x, sn = cs.y;
 #pragma unroll
@@ -115,7 +115,7 @@ __device__ __forceinline__ void svd4x4(double z[4][4], double v[4][4], double s[
           }
         }
       }
-    if (off < 1.0e-15) break;
+    if (done) break;
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -140,7 +140,7 @@ __device__ inline void eig4(double a[4][4], double e[4][4]) {
 #pragma unroll
       for (int j = i + 1; j < 4; ++j) off += a[i][j] * a[i][j];
     }
-    if (off <= 1.0e-34 * diag || off == 0.0) break;
+    if (off <= 1.0e-30 * diag || off == 0.0) break;      // off-diagonal norm below 1e-15 of the diagonal's
 #pragma unroll
     for (int p = 0; p < 3; ++p)
 #pragma unroll
