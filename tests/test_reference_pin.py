@@ -53,13 +53,13 @@ def _active(state):
     return np.ix_(idx, idx)
 
 
-def _same(ref, got, known):
+def _same(ref, got, known, state_tol=STATE_TOL):
     ra, rs, rS, rc = ref[:4]
     ga, gs, gS, gc = got[:4]
     if not known:
         assert [list(a) for a in ra] == [list(a) for a in ga]
         assert rc == gc
-    assert rel_fro(gs, rs) <= STATE_TOL
+    assert rel_fro(gs, rs) <= state_tol
     assert rel_fro(gS, rS) <= SIGMA_TOL
     blk = _active(rs)
     assert rel_fro(gS[blk], rS[blk]) <= ACTIVE_TOL
@@ -338,3 +338,61 @@ def test_cuda_small_prior_regime_is_tight_elementwise(name, fused):
     scans = [s for s in _scans(c) if c["known"] or len(s.xy)]
     ref = run_reference(scans, c["known"], c["N"], prior=1e2)
     _elementwise(ref, run_gpu(scans, c["known"], c["N"], fused=fused, prior=1e2), c["known"], NO_CANCEL_TOL)
+
+
+# ------------------------------------------------------------------------------------------------
+# seeded random configurations: capacity, field, drive, noise, gate and mode all vary with the seed
+def _random_case(seed):
+    rng = np.random.default_rng(1000 + seed)
+    known = bool(seed % 3 == 0)
+    n_field = int(rng.integers(3, 15))
+    N = int(n_field + rng.integers(2, 12))      # (an exactly full map makes the reference write past the end: pinned above)
+    field = synth.scattered_field(n_field, seed=200 + seed, extent=float(rng.uniform(2.5, 4.5)), min_sep=0.55)
+    kw = dict(n_scans=int(rng.integers(12, 36)), seed=300 + seed, landmarks=field, radius=float(rng.uniform(0.2, 0.5)),
+              slip=float(rng.uniform(0.0, 0.25)), sensor_std=float(10.0 ** rng.uniform(-3.3, -2.2)),
+              max_range=float(rng.uniform(1.2, 2.6)), theta0=float(rng.uniform(-3.0, 3.0)))
+    if not known:
+        kw.update(drop_out_of_range=True, shuffle=True)
+    filt = dict(q_noise=float(10.0 ** rng.uniform(-3.0, -1.7)), r_noise=float(10.0 ** rng.uniform(-2.5, -1.5)),
+                mah_threshold=float(rng.uniform(1.5, 4.0)))
+    scans = [s for s in synth.circle_drive(**kw) if known or len(s.xy)]
+    return scans, known, N, filt
+
+
+FUZZ_SEEDS = list(range(12))
+FUZZ_STATE_TOL = 1e-8     # the 1e7-prior cancellation reaches the state through the gain: 1.2e-9 on seed 9 (SURVEY 7.2 item 1
+                          # measured 4e-9 on its own probe); with a prior of 1e2 the same set-ups agree to 1e-11 element-wise
+
+
+def _fuzz_check(ref, got, known, prior):
+    if prior is None:
+        _same(ref, got, known, state_tol=FUZZ_STATE_TOL)
+    else:
+        _elementwise(ref, got, known, NO_CANCEL_TOL)
+
+
+@pytest.mark.parametrize("prior", [None, 1e2], ids=["prior_1e7", "prior_1e2"])
+@pytest.mark.parametrize("seed", FUZZ_SEEDS)
+def test_random_configurations_against_reference_source(seed, prior):
+    """oracle A, oracle B and the deferred model against the reference's object code on seeded random set-ups (map
+    capacity 5..25, 3..14 landmarks in the field, noise, slip, gate, process / sensor covariance, known or unknown
+    association).  At the reference's prior: association identical, Sigma 1e-9 norm-wise, observed block 1e-6, state
+    1e-8; with a prior of 1e2 (nothing cancels) the same set-ups: element-wise 1e-11."""
+    scans, known, N, filt = _random_case(seed)
+    pk = {} if prior is None else dict(prior=prior)
+    ref = run_reference(scans, known, N, prior=prior, **filt)
+    _fuzz_check(ref, run_literal(scans, known, N, **filt, **pk), known, prior)
+    _fuzz_check(ref, run_struct(scans, known, N, **filt, **pk), known, prior)
+    kw = dict(q=filt["q_noise"], r=filt["r_noise"], thr=filt["mah_threshold"])
+    _fuzz_check(ref, run_model(scans, known, N, **kw, **pk), known, prior)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prior", [None, 1e2], ids=["prior_1e7", "prior_1e2"])
+@pytest.mark.parametrize("seed", FUZZ_SEEDS)
+def test_cuda_random_configurations_against_reference_source(seed, prior):
+    from _harness import run_gpu
+    scans, known, N, filt = _random_case(seed)
+    pk = {} if prior is None else dict(prior=prior)
+    ref = run_reference(scans, known, N, prior=prior, **filt)
+    _fuzz_check(ref, run_gpu(scans, known, N, fused=bool(seed % 2), **filt, **pk), known, prior)
