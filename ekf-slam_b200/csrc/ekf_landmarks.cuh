@@ -1,6 +1,6 @@
 // Landmark extraction, the step right before the EKF hot path: a batch of
 // LaserScans -> clusters -> circle test -> algebraic circle fit -> (c_x, c_y, r) detections, i.e. the
-// sightings `ekf_update_unknown` consumes.  One warp per scan.
+// sightings `ekf_update_unknown` consumes.  Three kernels per batch of scans.
 //
 // Replaces, per scan,
 //   nuslam/src/landmarks.cpp:58-106    getClusters: beam -> (x, y) (lidar 0.032 m ahead of the base),
@@ -13,20 +13,21 @@
 //                                      Q = Y H^-1 Y, eigenvector of the smallest positive eigenvalue,
 //                                      A = Y^-1 A*   (arma::svd / eig_sym / solve in the reference)
 //
-// Shape (round 2; the ncu capture of the first shape - a thread per cluster rotating the n x 4 matrix Z in a
-// shared workspace - showed a latency-bound kernel: 10 warps per SM, 16 % of the issue slots, 16 cycles per
-// instruction, a third of the instructions in the Jacobi loops over the points):
-//   * the beams' (cos, sin) are the same for every scan of a launch: a table made once per call;
-//   * a cluster is still one thread (the factorizations are 4 wide), but Z is never stored: a modified
-//     Gram-Schmidt QR evaluated on the fly (five passes over the cluster's points, each recomputing the point's
-//     row of Z and its projections from px / py) leaves the 4 x 4 triangular factor R in registers, and the
-//     one-sided (Hestenes) Jacobi SVD runs on R - same singular values and right singular vectors as Z, R
-//     accurate to eps * |Z| like the reference's LAPACK path, 100 n instead of 340 n instructions per cluster;
-//   * the inscribed angles of the circle test are summed in one pass (shifted by the first angle), so they
-//     need no workspace either;
-//   * detections go straight to the output in cluster order (ballot + popcount, no staging).
-// Shared memory per scan is then px, py and the gap positions only (18 bytes per reading, 6.5 KB at 360 beams
-// instead of 20 KB), and resident scans per SM are bounded by registers (16 warps), not shared memory (10).
+// Shape (round 2, from three ncu captures of the earlier shapes - profiles/r2z_*, r2ac_*):
+//   1. ekf_landmarks_segment_kernel, a warp per scan: points (the beams' (cos, sin) are the same for every scan of a
+//      call: a table made once per call), gaps by a warp scan, and the clusters that pass the size filter appended to
+//      the batch's task list (one atomic per scan; a scan's tasks are contiguous and in cluster order);
+//   2. ekf_landmarks_fit_kernel, a THREAD per candidate cluster of the whole batch: circle test and fit.  A scan has
+//      only a handful of candidates, so with the fits inside the per-scan warp 3.8 of 32 lanes were active per
+//      instruction; here every lane of a warp holds a cluster (of whatever scan).  The points are re-evaluated from
+//      the ranges and the table wherever they are needed (same expression as in kernel 1: LmPoints::get); Z is never
+//      stored: a modified Gram-Schmidt QR evaluated on the fly (five passes over the cluster's points) leaves the
+//      4 x 4 triangular factor R in registers and the one-sided (Hestenes) Jacobi SVD runs on R - same singular
+//      values and right singular vectors as Z, accurate to eps * |Z| like the reference's LAPACK path; the
+//      inscribed angles of the circle test are summed in one pass (shifted by the first angle);
+//   3. ekf_landmarks_collect_kernel, a thread per scan: the kept detections in cluster order.
+// Code size matters here (divergent threads all over a long kernel): the Jacobi rotation scalars are one
+// __noinline__ copy and the loops over a cluster's points are not unrolled (109 -> 58 KB gave +32 %).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -35,9 +36,12 @@
 
 namespace ekf {
 
-constexpr int kLmThreads = 32;       // one warp per scan
+constexpr int kLmThreads = 32;       // segmentation: one warp per scan
 constexpr int kLmMaxPts = 39;        // clusters.at(i).size() < 40: landmarks.cpp:122
 constexpr int kLmErrNoGap = 3;       // the reference throws at clusters.at(0): landmarks.cpp:95
+
+// One cluster that reaches the circle test (4 .. 39 readings): which scan, and its readings as a ClusterView
+struct LmTask { int scan, start, len, tail0, tail; };
 
 struct LmParams {
   const float *ranges;     // [n_scans][n_ranges]
@@ -47,11 +51,33 @@ struct LmParams {
   double *out;             // [n_scans][max_out][3] (c_x, c_y, r), cluster order
   int *count;              // [n_scans] detections found (may exceed max_out; only max_out are stored)
   int *status;             // [n_scans] 0 or kLmErrNoGap
+  // between the three kernels of a call
+  LmTask *tasks;           // [task_cap] the batch's candidate clusters, each scan's contiguous and in cluster order
+  double4 *res;            // [task_cap] (c_x, c_y, r, keep) of each task
+  int *n_tasks;            // running total (zeroed before the call)
+  int *first_task;         // [n_scans] where the scan's tasks start
+  int *n_task_of;          // [n_scans] how many it has
+  int task_cap;
 };
 
 __host__ __device__ inline size_t lm_smem_bytes(int n_ranges) {
   return (size_t)n_ranges * (2 * sizeof(double) + sizeof(unsigned short)) + 16;
 }
+// a candidate cluster has at least four readings of its own
+__host__ __device__ inline int lm_max_tasks_per_scan(int n_ranges) { return n_ranges / 4 + 1; }
+
+// The readings of one scan as points in the robot frame (landmarks.cpp:66-69: the lidar sits 0.032 m ahead).  Both the
+// segmentation kernel and the fit kernel evaluate a point through this one expression.
+struct LmPoints {
+  const float *rg;
+  const double2 *beam;
+  __device__ __forceinline__ void get(int o, double &x, double &y) const {
+    const double r = (double)__ldg(rg + o);
+    const double2 cs = __ldg(beam + o);
+    x = r * cs.x - 0.032;
+    y = r * cs.y;
+  }
+};
 
 // landmarks.cpp:66-67: the angle of beam i, the same for every scan of a call
 __global__ void lm_beam_table_kernel(double2 *beam, int n, float angle_min, float angle_increment) {
@@ -171,17 +197,17 @@ __device__ inline void eig4(double a[4][4], double e[4][4]) {
 // z = x^2 + y^2) is reduced to its triangular factor R by modified Gram-Schmidt without being stored: pass c
 // recomputes, per point, the row of Z and what the earlier columns left of it, and accumulates column c's norm
 // and its products with the later columns.  The SVD of R gives Z's singular values and V.
-__device__ inline void fit_circle(const double *px, const double *py, const ClusterView &cv, int n, double &cx,
-                                  double &cy, double &R) {
+__device__ inline void fit_circle(const LmPoints &P, const ClusterView &cv, int n, double &cx, double &cy, double &R) {
   double mx = 0.0, my = 0.0;
 #pragma unroll 1
-  for (int i = 0; i < n; ++i) { const int o = cv.at(i); mx += px[o]; my += py[o]; }
+  for (int i = 0; i < n; ++i) { double x, y; P.get(cv.at(i), x, y); mx += x; my += y; }
   mx /= n; my /= n;
   double s00 = 0.0, s01 = 0.0, s02 = 0.0, s03 = 0.0;
 #pragma unroll 1
   for (int i = 0; i < n; ++i) {
-    const int o = cv.at(i);
-    const double xi = px[o] - mx, yi = py[o] - my;
+    double x, y;
+    P.get(cv.at(i), x, y);
+    const double xi = x - mx, yi = y - my;
     const double z0 = xi * xi + yi * yi;
     s00 += z0 * z0; s01 += z0 * xi; s02 += z0 * yi; s03 += z0;
   }
@@ -191,8 +217,9 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
   double s11 = 0.0, s12 = 0.0, s13 = 0.0;
 #pragma unroll 1
   for (int i = 0; i < n; ++i) {
-    const int o = cv.at(i);
-    const double xi = px[o] - mx, yi = py[o] - my;
+    double x, y;
+    P.get(cv.at(i), x, y);
+    const double xi = x - mx, yi = y - my;
     const double q0 = (xi * xi + yi * yi) * i0;
     const double a1 = xi - r01 * q0, a2 = yi - r02 * q0, a3 = 1.0 - r03 * q0;
     s11 += a1 * a1; s12 += a1 * a2; s13 += a1 * a3;
@@ -202,8 +229,9 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
   double s22 = 0.0, s23 = 0.0;
 #pragma unroll 1
   for (int i = 0; i < n; ++i) {
-    const int o = cv.at(i);
-    const double xi = px[o] - mx, yi = py[o] - my;
+    double x, y;
+    P.get(cv.at(i), x, y);
+    const double xi = x - mx, yi = y - my;
     const double q0 = (xi * xi + yi * yi) * i0;
     const double a1 = xi - r01 * q0, a2 = yi - r02 * q0, a3 = 1.0 - r03 * q0;
     const double q1 = a1 * i1;
@@ -215,8 +243,9 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
   double s33 = 0.0;
 #pragma unroll 1
   for (int i = 0; i < n; ++i) {
-    const int o = cv.at(i);
-    const double xi = px[o] - mx, yi = py[o] - my;
+    double x, y;
+    P.get(cv.at(i), x, y);
+    const double xi = x - mx, yi = y - my;
     const double q0 = (xi * xi + yi * yi) * i0;
     const double a1 = xi - r01 * q0, a2 = yi - r02 * q0, a3 = 1.0 - r03 * q0;
     const double q1 = a1 * i1;
@@ -316,15 +345,17 @@ __device__ inline void fit_circle(const double *px, const double *py, const Clus
 
 // turtlelib/src/landmark_detection.cpp:5-48.  Mean and N-1 standard deviation of the inscribed angles in one pass
 // (sums of the angles' differences from the first one: no cancellation to speak of, no workspace)
-__device__ inline bool check_circle(const double *px, const double *py, const ClusterView &cv, int n) {
-  const int o0 = cv.at(0), oe = cv.at(n - 1);
-  const double sx = px[o0], sy = py[o0], ex = px[oe], ey = py[oe];
+__device__ inline bool check_circle(const LmPoints &P, const ClusterView &cv, int n) {
+  double sx, sy, ex, ey;
+  P.get(cv.at(0), sx, sy);
+  P.get(cv.at(n - 1), ex, ey);
   const double c = sqrt(sq_sum(sx - ex, sy - ey));
   double first = 0.0, sd = 0.0, sd2 = 0.0;
 #pragma unroll 1
   for (int j = 1; j < n - 1; ++j) {
-    const int o = cv.at(j);
-    const double a = sqrt(sq_sum(sx - px[o], sy - py[o])), b = sqrt(sq_sum(ex - px[o], ey - py[o]));
+    double x, y;
+    P.get(cv.at(j), x, y);
+    const double a = sqrt(sq_sum(sx - x, sy - y)), b = sqrt(sq_sum(ex - x, ey - y));
     const double an = acos((c * c - a * a - b * b) / (-2.0 * a * b));
     if (j == 1) first = an;
     const double d = an - first;
@@ -337,8 +368,8 @@ __device__ inline bool check_circle(const double *px, const double *py, const Cl
   return stdev < 0.2 && 1.3 < mn && mn < 2.6;
 }
 
-// (16 resident scans per SM: 128 registers; sized for 20 or 24 it spills and is no faster - measured)
-__global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmParams p) {
+// ---- kernel 1 of 3: segmentation, one warp per scan -> the scan's candidate clusters as tasks --------------------
+__global__ void __launch_bounds__(kLmThreads) ekf_landmarks_segment_kernel(const LmParams p) {
   extern __shared__ __align__(16) unsigned char lm_smem[];
   const int n = p.n_ranges;
   double *px = reinterpret_cast<double *>(lm_smem);
@@ -346,15 +377,9 @@ __global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmP
   unsigned short *gpos = reinterpret_cast<unsigned short *>(py + n);   // gap positions, in order (n <= 4096)
   const int scan = blockIdx.x, lane = threadIdx.x;
   if (scan >= p.n_scans) return;
-  const float *rg = p.ranges + (size_t)scan * n;
+  const LmPoints P{p.ranges + (size_t)scan * n, p.beam};
 
-  // landmarks.cpp:66-69
-  for (int i = lane; i < n; i += kLmThreads) {
-    const double r = (double)rg[i];
-    const double2 cs = p.beam[i];
-    px[i] = r * cs.x - 0.032;
-    py[i] = r * cs.y;
-  }
+  for (int i = lane; i < n; i += kLmThreads) P.get(i, px[i], py[i]);
   __syncwarp();
 
   // gaps (landmarks.cpp:75-86), ordered positions by a warp scan over contiguous per-lane slices
@@ -380,43 +405,84 @@ __global__ void __launch_bounds__(kLmThreads, 16) ekf_landmarks_kernel(const LmP
   __syncwarp();
 
   if (G == 0) {                         // clusters.at(0) throws in the reference (landmarks.cpp:95)
-    if (lane == 0) { p.count[scan] = 0; p.status[scan] = kLmErrNoGap; }
+    if (lane == 0) { p.first_task[scan] = 0; p.n_task_of[scan] = 0; p.status[scan] = kLmErrNoGap; }
     return;
   }
   const bool wrap = sqrt(sq_sum(px[0] - px[n - 1], py[0] - py[n - 1])) <= p.thr;   // landmarks.cpp:93-103
   const int n_clusters = wrap ? G : G + 1;
+  const int tail0 = (int)gpos[G - 1] + 1;
 
-  // one lane per cluster: size filter, circle test, fit, final filter (landmarks.cpp:117-149); detections leave in
-  // cluster order (marker id = running index, :137-148)
+  // the clusters that pass the size filter (landmarks.cpp:122: more than 3, fewer than 40 readings), in cluster order:
+  // counted, then written behind a base taken from the batch's running total
+  auto view = [&](int k, ClusterView &cv, int &tail) {
+    cv.start = (k == 0) ? 0 : (int)gpos[k - 1] + 1;
+    const int end = (k < G) ? (int)gpos[k] : n;                  // exclusive
+    cv.len = end - cv.start;
+    cv.tail0 = tail0;
+    tail = (k == 0 && wrap) ? n - tail0 : 0;
+    const int total = cv.len + tail;
+    return total > 3 && total <= kLmMaxPts;
+  };
+  int n_cand = 0;
+  for (int base = 0; base < n_clusters; base += kLmThreads) {
+    ClusterView cv; int tail;
+    const bool cand = base + lane < n_clusters && view(base + lane, cv, tail);
+    n_cand += __popc(__ballot_sync(0xffffffffu, cand));
+  }
+  int first = 0;
+  if (lane == 0 && n_cand > 0) first = atomicAdd(p.n_tasks, n_cand);
+  first = __shfl_sync(0xffffffffu, first, 0);
+  if (first + n_cand > p.task_cap) n_cand = max(0, p.task_cap - first);   // (cannot happen: the capacity is the bound)
   int written = 0;
   for (int base = 0; base < n_clusters; base += kLmThreads) {
-    const int k = base + lane;
-    bool keep = false;
-    double cx = 0.0, cy = 0.0, R = 0.0;
-    if (k < n_clusters) {
-      ClusterView cv;
-      cv.start = (k == 0) ? 0 : (int)gpos[k - 1] + 1;
-      const int end = (k < G) ? (int)gpos[k] : n;                // exclusive
-      cv.len = end - cv.start;
-      cv.tail0 = (int)gpos[G - 1] + 1;
-      const int tail = (k == 0 && wrap) ? n - cv.tail0 : 0;
-      const int total = cv.len + tail;
-      if (total > 3 && total <= kLmMaxPts) {
-        if (check_circle(px, py, cv, total)) {
-          fit_circle(px, py, cv, total, cx, cy, R);
-          keep = R < 0.2 && sqrt(sq_sum(cx, cy)) < 2.0;
-        }
-      }
-    }
-    const unsigned km = __ballot_sync(0xffffffffu, keep);
-    const int orank = written + __popc(km & ((1u << lane) - 1u));
-    if (keep && orank < p.max_out) {
-      double *d = p.out + ((size_t)scan * p.max_out + orank) * 3;
-      d[0] = cx; d[1] = cy; d[2] = R;
-    }
-    written += __popc(km);
+    ClusterView cv; int tail;
+    const bool cand = base + lane < n_clusters && view(base + lane, cv, tail);
+    const unsigned cm = __ballot_sync(0xffffffffu, cand);
+    const int j = written + __popc(cm & ((1u << lane) - 1u));
+    if (cand && j < n_cand) p.tasks[first + j] = LmTask{scan, cv.start, cv.len, cv.tail0, tail};
+    written += __popc(cm);
   }
-  if (lane == 0) { p.count[scan] = written; p.status[scan] = 0; }
+  if (lane == 0) { p.first_task[scan] = first; p.n_task_of[scan] = n_cand; p.status[scan] = 0; }
+}
+
+// ---- kernel 2 of 3: circle test + fit, one THREAD per candidate cluster of the whole batch ---------------------------
+// (A scan has only a handful of candidates: with the fits inside the per-scan warp 3.8 of 32 lanes were active per
+// instruction.  Here the lanes of a warp hold clusters of different scans and all of them work.)
+constexpr int kLmFitThreads = 128;
+__global__ void __launch_bounds__(kLmFitThreads, 4) ekf_landmarks_fit_kernel(const LmParams p) {
+  const int total = min(*p.n_tasks, p.task_cap);
+  for (int t = blockIdx.x * kLmFitThreads + threadIdx.x; t < total; t += gridDim.x * kLmFitThreads) {
+    const LmTask task = p.tasks[t];
+    const LmPoints P{p.ranges + (size_t)task.scan * p.n_ranges, p.beam};
+    ClusterView cv;
+    cv.start = task.start; cv.len = task.len; cv.tail0 = task.tail0;
+    const int n_pts = task.len + task.tail;
+    double cx = 0.0, cy = 0.0, R = 0.0, keep = 0.0;
+    if (check_circle(P, cv, n_pts)) {                            // landmarks.cpp:124-149
+      fit_circle(P, cv, n_pts, cx, cy, R);
+      if (R < 0.2 && sqrt(sq_sum(cx, cy)) < 2.0) keep = 1.0;
+    }
+    p.res[t] = make_double4(cx, cy, R, keep);
+  }
+}
+
+// ---- kernel 3 of 3: the kept detections of every scan, in cluster order (marker id = running index, :137-148) ----------
+__global__ void ekf_landmarks_collect_kernel(const LmParams p) {
+  const int scan = blockIdx.x * blockDim.x + threadIdx.x;
+  if (scan >= p.n_scans) return;
+  const int first = p.first_task[scan], cnt = p.n_task_of[scan];
+  int written = 0;
+  for (int j = 0; j < cnt; ++j) {
+    const double4 r = p.res[first + j];
+    if (r.w != 0.0) {
+      if (written < p.max_out) {
+        double *d = p.out + ((size_t)scan * p.max_out + written) * 3;
+        d[0] = r.x; d[1] = r.y; d[2] = r.z;
+      }
+      ++written;
+    }
+  }
+  p.count[scan] = written;
 }
 
 }  // namespace ekf
