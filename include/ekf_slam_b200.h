@@ -273,7 +273,7 @@ int ekf_batch_step_bytes(ekf_batch *b, int32_t m, int64_t *bytes);
  * A batch of LaserScans (float ranges, n_ranges beams each, as in sensor_msgs/LaserScan) ->
  * per scan the circle detections (c_x, c_y, r) in the lidar-corrected robot frame, in cluster order:
  * what nuslam's `landmarks` node publishes on green/detected_obstacles (nuslam/src/landmarks.cpp:58-156
- * with turtlelib checkCircle / fitCircle, turtlelib/src/landmark_detection.cpp:5-135).  One warp per scan.
+ * with turtlelib checkCircle / fitCircle, turtlelib/src/landmark_detection.cpp:5-135).  n_scans <= max_scans of the handle.
  * out_xyr[n_scans][max_out][3]; out_count[s] = detections of scan s (only the first max_out are stored);
  * out_status[s] = 0, or EKF_ERR_EMPTY_SCAN when the scan has no range discontinuity at all (the
  * reference throws at clusters.at(0), landmarks.cpp:95).  cluster_threshold = 0.2 in the reference.

@@ -4,7 +4,7 @@ CPU oracles on a bounded sample (which is why this script lives under tests/: on
 cpu_baseline may execute oracle/).  One JSON object on stdout:
 
   N2 lidar        nusim.cpp:559-710   one thread per (robot, beam)        ekf_nusim_lidar_dev
-  N1 landmarks    landmarks.cpp:58-156 one warp per 360-beam LaserScan     ekf_landmarks_detect_dev
+  N1 landmarks    landmarks.cpp:58-156 warp per scan + thread per cluster   ekf_landmarks_detect_dev
   N2 fake sensor  nusim.cpp:310-349   one thread per (robot, obstacle)    ekf_nusim_fake_sensor_dev
   chain           lidar -> landmarks without leaving the device (the Monte-Carlo producer loop)
 
